@@ -1,0 +1,114 @@
+// common.cuh -- context, error handling and workspace for libhmj.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/hmj.h"
+
+#define HMJ_NUM_SMS_HINT 148
+
+// Named scratch slots of the context workspace (grow-only, reused across calls so that no
+// cudaMalloc happens in a steady-state timed region).
+enum hmj_ws_slot {
+  WS_HIST = 0,      // digit histograms / bin offsets
+  WS_LOOKBACK,      // decoupled look-back tile descriptors
+  WS_SORT_KEYS_A,   // ping-pong buffers of the sort
+  WS_SORT_VALS_A,
+  WS_SORT_KEYS_B,
+  WS_SORT_VALS_B,
+  WS_R_HASH,        // whole-operator: sorted columns of R and S
+  WS_R_ROWID,
+  WS_S_HASH,
+  WS_S_ROWID,
+  WS_JOIN_TILES,    // merge-path partition points + per-tile counts
+  WS_JOIN_MISC,
+  WS_OUT_R,         // whole-operator: result pairs
+  WS_OUT_S,
+  WS_IN_0,          // host-entry staging of inputs
+  WS_IN_1,
+  WS_IN_2,
+  WS_IN_3,
+  WS_TABLE,         // hash-join baseline table
+  WS_SCALARS,       // small device scalars (counters, sums)
+  WS_NUM_SLOTS
+};
+
+struct hmj_buf {
+  void* ptr = nullptr;
+  size_t bytes = 0;
+};
+
+struct hmj_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int num_sms = HMJ_NUM_SMS_HINT;
+  std::string err;
+  hmj_buf ws[WS_NUM_SLOTS];
+  void* pinned = nullptr;  // small pinned host scratch for scalar read-backs
+  size_t pinned_bytes = 0;
+  uint64_t launches = 0;
+  // last whole-operator result
+  uint64_t last_pairs = 0;
+  hmj_timings tm;
+  cudaEvent_t ev[8] = {};
+};
+
+static inline int hmj_fail(hmj_ctx* ctx, int code, const char* what, const char* file, int line) {
+  if (ctx) {
+    char b[512];
+    snprintf(b, sizeof b, "%s (%s:%d)", what, file, line);
+    ctx->err = b;
+  }
+  return code;
+}
+
+#define HMJ_CUDA(ctx, call)                                                        \
+  do {                                                                             \
+    cudaError_t e__ = (call);                                                      \
+    if (e__ != cudaSuccess) {                                                      \
+      return hmj_fail(ctx, e__ == cudaErrorMemoryAllocation ? HMJ_ENOMEM : HMJ_ECUDA, \
+                      cudaGetErrorString(e__), __FILE__, __LINE__);                \
+    }                                                                              \
+  } while (0)
+
+#define HMJ_TRY(expr)            \
+  do {                           \
+    int rc__ = (expr);           \
+    if (rc__ != HMJ_OK) return rc__; \
+  } while (0)
+
+#define HMJ_ARG(ctx, cond)                                                   \
+  do {                                                                       \
+    if (!(cond)) return hmj_fail(ctx, HMJ_EARG, "bad argument: " #cond, __FILE__, __LINE__); \
+  } while (0)
+
+// checks the launch itself (not completion) and counts it
+#define HMJ_LAUNCHED(ctx)                 \
+  do {                                    \
+    (ctx)->launches++;                    \
+    HMJ_CUDA(ctx, cudaGetLastError());    \
+  } while (0)
+
+// returns a device scratch buffer of at least `bytes` bytes in slot `slot`
+int hmj_ws_get(hmj_ctx* ctx, int slot, size_t bytes, void** out);
+
+template <typename T>
+static inline int hmj_ws(hmj_ctx* ctx, int slot, size_t count, T** out) {
+  void* p = nullptr;
+  int rc = hmj_ws_get(ctx, slot, count * sizeof(T), &p);
+  *out = reinterpret_cast<T*>(p);
+  return rc;
+}
+
+static inline size_t hmj_div_up(size_t a, size_t b) { return (a + b - 1) / b; }
+
+// ---- stage entry points shared between translation units -----------------------------
+// (implemented in hash.cu / radix_sort.cu / merge_join.cu / hash_table.cu / partition.cu)
+int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* d_keys_in, const uint32_t* d_vals_in, size_t n,
+                  uint64_t* d_keys_out, uint32_t* d_vals_out);

@@ -1,0 +1,190 @@
+/*
+ * hmj.h -- C ABI of libhmj.so, the B200 (sm_100a) hash -> radix-sort -> merge-join path.
+ *
+ * This is the drop-in boundary for the hot path of dryman/HashMergeJoin.  The reference has
+ * no FFI: its interface is C++11 header templates.  Each entry point below names the reference
+ * template/loop it stands in for; the C++ facade headers in hashmergejoin_b200/facade/
+ * (radix_hash.h, hashjoin.h, partitioned_hash.h, radix_sort.h) keep the reference's names and
+ * argument order and call only these functions.
+ *
+ * Conventions
+ *  - every function returns an int status: HMJ_OK (0) or a negative HMJ_E* code;
+ *    hmj_last_error(ctx) gives the text.  There is NO CPU fallback: without a usable CUDA
+ *    device hmj_create fails with HMJ_ENODEVICE.
+ *  - pointers named d_* are DEVICE pointers (HBM of the context's device); pointers named
+ *    h_* are HOST pointers (pageable or pinned).  Sizes are element counts unless "bytes".
+ *  - relations are columnar: integer keys as u64[n]; string keys as offsets u64[n+1] into a
+ *    chars byte buffer (row i = chars[offsets[i] .. offsets[i+1])).  Row ids are u32, so a
+ *    relation has at most 2^32-1 rows (the reference caps n at 2^31-1, radix_hash.h:361).
+ *  - all calls are asynchronous on the context's stream unless they return a scalar to the
+ *    host (then they synchronise that stream).  One context = one device + one stream;
+ *    a context is not thread-safe.
+ */
+#ifndef HMJ_H
+#define HMJ_H 1
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HMJ_OK 0
+#define HMJ_EARG (-1)       /* bad argument */
+#define HMJ_ECUDA (-2)      /* CUDA runtime error */
+#define HMJ_ENOMEM (-3)     /* device or host allocation failed */
+#define HMJ_ENODEVICE (-4)  /* no CUDA device / wrong architecture */
+#define HMJ_ECAPACITY (-5)  /* caller-provided output capacity too small */
+
+typedef struct hmj_ctx hmj_ctx;
+
+/* key description used by the join / hash-table entry points */
+#define HMJ_KEY_U64 0     /* std::hash<integral> = identity: hash equality == key equality */
+#define HMJ_KEY_STRING 1  /* std::hash<std::string>: verify key bytes on every hash match */
+
+/* ---- context ------------------------------------------------------------------------- */
+/* Creates a context on `device` with its own non-blocking stream. */
+int hmj_create(hmj_ctx** ctx, int device);
+/* Same, but work is issued on the caller's cudaStream_t (e.g. torch's current stream). */
+int hmj_create_on_stream(hmj_ctx** ctx, int device, void* cuda_stream);
+int hmj_destroy(hmj_ctx* ctx);
+const char* hmj_last_error(hmj_ctx* ctx);
+int hmj_synchronize(hmj_ctx* ctx);
+/* library/version probe usable without a GPU (returns e.g. "hmj-b200 0.1 sm_100a"). */
+const char* hmj_version(void);
+/* number of kernels launched by this context since creation (for bench gpu_launches). */
+int hmj_launch_count(hmj_ctx* ctx, uint64_t* count);
+/* releases the cached workspace (scratch buffers grow on demand and are reused). */
+int hmj_release_workspace(hmj_ctx* ctx);
+
+/* ---- A9: radix width helper ---------------------------------------------------------- */
+/* replaces radix_hash::optimal_partition (radix_hash.h:38-57); host scalar, no GPU needed. */
+int hmj_optimal_partition(size_t input_num);
+
+/* ---- A1: hashing --------------------------------------------------------------------- */
+/* replaces Hash{}(key) with Hash = std::hash<integral> (identity) at radix_hash.h:314,340 */
+int hmj_hash_u64(hmj_ctx* ctx, const uint64_t* d_keys, size_t n, uint64_t* d_hash);
+/* replaces Hash{}(key) with Hash = std::hash<std::string> (libstdc++ _Hash_bytes, seed
+ * 0xc70f6907) at radix_hash.h:314,340 and partitioned_hash.h:58,76 */
+int hmj_hash_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const uint8_t* d_chars,
+                     size_t n, uint64_t* d_hash);
+
+/* ---- A2+A3+A4: sort of (hash,row-id) pairs ------------------------------------------- */
+/* replaces radix_hash::radix_inplace_seq / radix_inplace_par (radix_hash.h:425-654) on a
+ * pre-hashed column.  Sorts d_hash ascending, permuting d_rowid alongside; the sort is stable,
+ * so equal hashes keep ascending input order.  d_rowid == NULL on input means "iota": pass
+ * d_rowid_out to receive the permutation.  Results are left in d_hash_out / d_rowid_out
+ * (may alias the inputs). */
+int hmj_sort_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid, size_t n,
+                   uint64_t* d_hash_out, uint32_t* d_rowid_out);
+/* replaces radix_hash::radix_non_inplace_par<Key,Value,std::hash<Key>> (radix_hash.h:351-423):
+ * hash + sort in one call; row id = input index. */
+int hmj_hash_sort_u64(hmj_ctx* ctx, const uint64_t* d_keys, size_t n, uint64_t* d_hash_out,
+                      uint32_t* d_rowid_out);
+int hmj_hash_sort_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const uint8_t* d_chars,
+                          size_t n, uint64_t* d_hash_out, uint32_t* d_rowid_out);
+/* replaces ::radix_int_inplace / ::radix_int_non_inplace (radix_sort.h:333-398,452-522):
+ * sort of (unsigned key, u32 payload) pairs without hashing.  Same kernel as hmj_sort_pairs. */
+int hmj_sort_int_pairs(hmj_ctx* ctx, const uint64_t* d_keys, const uint32_t* d_vals, size_t n,
+                       uint64_t* d_keys_out, uint32_t* d_vals_out);
+
+/* ---- A5: merge join of two sorted (hash,row-id) streams ------------------------------ */
+/* A relation as the join sees it: the sorted pairs plus (for strings) the key storage the
+ * row ids point into, used for full-key verification on every hash match. */
+typedef struct hmj_relation {
+  const uint64_t* d_hash;    /* sorted ascending, n entries */
+  const uint32_t* d_rowid;   /* row id of each sorted entry */
+  size_t n;
+  int key_kind;              /* HMJ_KEY_U64 or HMJ_KEY_STRING */
+  const uint64_t* d_offsets; /* HMJ_KEY_STRING: n+1 offsets (indexed by row id) */
+  const uint8_t* d_chars;    /* HMJ_KEY_STRING: key bytes */
+} hmj_relation;
+
+/* replaces the merge walk of HashMergeJoin::iterator (hashjoin.h:70-180) as a TRUE equi-join:
+ * every (r,s) with equal hash and equal key.  Pass 1: exact number of matching pairs. */
+int hmj_merge_join_count(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+                         uint64_t* h_num_pairs);
+/* Pass 2: writes the pairs as (build_row = R row id, probe_row = S row id) into two u32
+ * device arrays of capacity `cap` pairs; *h_num_pairs receives the count written.
+ * Returns HMJ_ECAPACITY (nothing written beyond cap) when cap is too small. */
+int hmj_merge_join_write(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+                         uint32_t* d_out_r, uint32_t* d_out_s, size_t cap,
+                         uint64_t* h_num_pairs);
+/* the consumer of hashjoin_bench.cc:131-133: count and sum += r.value + s.value over all
+ * matches, without materialising pairs.  d_rvals/d_svals are u64 payload columns indexed by
+ * row id; NULL means "payload = row id". */
+int hmj_merge_join_aggregate(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+                             const uint64_t* d_rvals, const uint64_t* d_svals,
+                             uint64_t* h_num_pairs, uint64_t* h_sum);
+
+/* ---- whole operator: HashMergeJoin(r_begin,r_end,s_begin,s_end) ----------------------- */
+/* replaces HashMergeJoin ctor + full iteration (hashjoin.h:56-68,183-195) with DEVICE inputs.
+ * Hash both sides, sort both, merge-join; the result stays in context-owned device buffers
+ * until the next join on this context.  *h_num_pairs receives the pair count. */
+int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr, const uint64_t* d_skeys,
+                 size_t ns, uint64_t* h_num_pairs);
+int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
+                     size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars, size_t ns,
+                     uint64_t* h_num_pairs);
+/* device pointers to the last join's pairs (valid until the next join / destroy). */
+int hmj_join_result(hmj_ctx* ctx, const uint32_t** d_out_r, const uint32_t** d_out_s,
+                    uint64_t* num_pairs);
+/* copies the last join's pairs to host arrays of capacity cap. */
+int hmj_join_result_to_host(hmj_ctx* ctx, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap);
+
+/* Same operator with HOST buffers: H2D copies, join and D2H of the pairs inside the call.
+ * This is what the C++ facade and the e2e benchmark call. h_out_* may be NULL (count only). */
+int hmj_join_u64_host(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, const uint64_t* h_skeys,
+                      size_t ns, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap,
+                      uint64_t* h_num_pairs);
+int hmj_join_strings_host(hmj_ctx* ctx, const uint64_t* h_roffsets, const uint8_t* h_rchars,
+                          size_t nr, const uint64_t* h_soffsets, const uint8_t* h_schars,
+                          size_t ns, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap,
+                          uint64_t* h_num_pairs);
+/* host-buffer versions of the sort entry points (facade: radix_non_inplace_par etc.). */
+int hmj_hash_sort_u64_host(hmj_ctx* ctx, const uint64_t* h_keys, size_t n, uint64_t* h_hash_out,
+                           uint32_t* h_rowid_out);
+int hmj_hash_sort_strings_host(hmj_ctx* ctx, const uint64_t* h_offsets, const uint8_t* h_chars,
+                               size_t n, uint64_t* h_hash_out, uint32_t* h_rowid_out);
+int hmj_sort_pairs_host(hmj_ctx* ctx, const uint64_t* h_hash, const uint32_t* h_rowid, size_t n,
+                        uint64_t* h_hash_out, uint32_t* h_rowid_out);
+
+/* ---- A6: partitioning on the top hash bits ------------------------------------------- */
+/* replaces the counting loop of partition_only (partitioned_hash.h:57-60): counts[p] = number
+ * of rows with (hash >> (64-bits)) == p; d_counts has 1<<bits u64 entries. bits in [1,16]. */
+int hmj_partition_counts(hmj_ctx* ctx, const uint64_t* d_hash, size_t n, int bits,
+                         uint64_t* d_counts);
+/* replaces the scatter of partition_only (partitioned_hash.h:75-79), deterministically:
+ * rows are grouped by partition, stable inside a partition.  d_rowid NULL = iota.
+ * d_part_offsets receives (1<<bits)+1 u64 exclusive offsets.  bits in [1,8]. */
+int hmj_partition_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid, size_t n,
+                        int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
+                        uint64_t* d_part_offsets);
+int hmj_partition_counts_host(hmj_ctx* ctx, const uint64_t* h_hash, size_t n, int bits,
+                              uint64_t* h_counts);
+
+/* ---- A7: hash-join baseline (build/probe) -------------------------------------------- */
+/* replaces the loops of BM_hash_join_raw (hashjoin_bench.cc:47-53): build an open-addressing
+ * table over S (duplicate keys: last row wins, as s_map[k]=v), probe with every R row and
+ * return sum += r.value + (hit ? s.value : 0) and the number of hits.  d_*vals NULL = row id. */
+int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r_unsorted,
+                             const hmj_relation* s_unsorted, const uint64_t* d_rvals,
+                             const uint64_t* d_svals, uint64_t* h_hits, uint64_t* h_sum);
+
+/* ---- per-stage device timings of the last whole-operator call ------------------------ */
+typedef struct hmj_timings {
+  float hash_ms;       /* K1 */
+  float histogram_ms;  /* K2 */
+  float sort_ms;       /* K3 (all passes, both relations) */
+  float join_ms;       /* K4-K6 */
+  float h2d_ms, d2h_ms;
+  float total_ms;
+  uint32_t sort_passes; /* scatter passes actually executed (both relations) */
+} hmj_timings;
+int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HMJ_H */
