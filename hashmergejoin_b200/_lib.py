@@ -1,0 +1,104 @@
+"""ctypes binding of libhmj.so (the C ABI declared in include/hmj.h).
+
+There is no fallback of any kind: if the CUDA library has not been built (``make lib`` or
+``__graft_entry__.build()``) importing the binding raises, and every call that returns a
+non-zero status raises :class:`HmjError` with the library's own message.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhmj.so")
+
+HMJ_OK = 0
+HMJ_EARG, HMJ_ECUDA, HMJ_ENOMEM, HMJ_ENODEVICE, HMJ_ECAPACITY = -1, -2, -3, -4, -5
+KEY_U64, KEY_STRING = 0, 1
+
+_STATUS = {
+    HMJ_EARG: "HMJ_EARG", HMJ_ECUDA: "HMJ_ECUDA", HMJ_ENOMEM: "HMJ_ENOMEM",
+    HMJ_ENODEVICE: "HMJ_ENODEVICE", HMJ_ECAPACITY: "HMJ_ECAPACITY",
+}
+
+
+class HmjError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"{_STATUS.get(code, code)}: {msg}")
+        self.code = code
+
+
+class Relation(C.Structure):
+    """struct hmj_relation"""
+    _fields_ = [
+        ("d_hash", C.c_void_p), ("d_rowid", C.c_void_p), ("n", C.c_size_t),
+        ("key_kind", C.c_int), ("d_offsets", C.c_void_p), ("d_chars", C.c_void_p),
+    ]
+
+
+class Timings(C.Structure):
+    """struct hmj_timings"""
+    _fields_ = [
+        ("hash_ms", C.c_float), ("histogram_ms", C.c_float), ("sort_ms", C.c_float),
+        ("join_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
+        ("total_ms", C.c_float), ("sort_passes", C.c_uint32),
+    ]
+
+
+_P, _SZ, _I = C.c_void_p, C.c_size_t, C.c_int
+_U64P = C.POINTER(C.c_uint64)
+_RELP = C.POINTER(Relation)
+
+# name -> (restype, argtypes); must list every function include/hmj.h declares
+SIGNATURES = {
+    "hmj_create": (_I, [C.POINTER(_P), _I]),
+    "hmj_create_on_stream": (_I, [C.POINTER(_P), _I, _P]),
+    "hmj_destroy": (_I, [_P]),
+    "hmj_last_error": (C.c_char_p, [_P]),
+    "hmj_synchronize": (_I, [_P]),
+    "hmj_version": (C.c_char_p, []),
+    "hmj_launch_count": (_I, [_P, _U64P]),
+    "hmj_release_workspace": (_I, [_P]),
+    "hmj_optimal_partition": (_I, [_SZ]),
+    "hmj_hash_u64": (_I, [_P, _P, _SZ, _P]),
+    "hmj_hash_strings": (_I, [_P, _P, _P, _SZ, _P]),
+    "hmj_sort_pairs": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_hash_sort_u64": (_I, [_P, _P, _SZ, _P, _P]),
+    "hmj_hash_sort_strings": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_sort_int_pairs": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_merge_join_count": (_I, [_P, _RELP, _RELP, _U64P]),
+    "hmj_merge_join_write": (_I, [_P, _RELP, _RELP, _P, _P, _SZ, _U64P]),
+    "hmj_merge_join_aggregate": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),
+    "hmj_join_u64": (_I, [_P, _P, _SZ, _P, _SZ, _U64P]),
+    "hmj_join_strings": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
+    "hmj_join_result": (_I, [_P, C.POINTER(_P), C.POINTER(_P), _U64P]),
+    "hmj_join_result_to_host": (_I, [_P, _P, _P, _SZ]),
+    "hmj_join_u64_host": (_I, [_P, _P, _SZ, _P, _SZ, _P, _P, _SZ, _U64P]),
+    "hmj_join_strings_host": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
+    "hmj_hash_sort_u64_host": (_I, [_P, _P, _SZ, _P, _P]),
+    "hmj_hash_sort_strings_host": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_sort_pairs_host": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_partition_counts": (_I, [_P, _P, _SZ, _I, _P]),
+    "hmj_partition_pairs": (_I, [_P, _P, _P, _SZ, _I, _P, _P, _P]),
+    "hmj_partition_counts_host": (_I, [_P, _P, _SZ, _I, _P]),
+    "hmj_hashjoin_build_probe": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),
+    "hmj_get_timings": (_I, [_P, C.POINTER(Timings)]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libhmj.so (once). Raises ImportError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make lib` (or __graft_entry__.build()). "
+            "hashmergejoin_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header/library mismatch
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

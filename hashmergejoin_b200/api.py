@@ -1,0 +1,246 @@
+"""Host-side Python plumbing over the C ABI: device memory comes from torch tensors, host
+buffers from numpy arrays.  Nothing here computes: every method is one C-ABI call into the CUDA
+library (hashmergejoin_b200/csrc).  Columns are u64/u32; torch has no arithmetic on unsigned
+64-bit, so device columns are int64/int32 tensors that are reinterpreted, never converted.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import KEY_STRING, KEY_U64, HmjError, Relation, Timings
+
+
+def _dptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _hptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def _check_dev(t, dtype_bytes):
+    assert t.is_cuda and t.is_contiguous() and t.element_size() == dtype_bytes, \
+        "expected a contiguous CUDA tensor of %d-byte elements" % dtype_bytes
+
+
+class SortedRelation:
+    """Sorted (hash,row-id) columns of one relation plus the key storage the row ids point to."""
+
+    def __init__(self, hash_, rowid, kind=KEY_U64, offsets=None, chars=None):
+        self.hash, self.rowid, self.kind = hash_, rowid, kind
+        self.offsets, self.chars = offsets, chars
+
+    def as_struct(self):
+        r = Relation()
+        r.d_hash = self.hash.data_ptr()
+        r.d_rowid = self.rowid.data_ptr() if self.rowid is not None else None
+        r.n = self.hash.numel()
+        r.key_kind = self.kind
+        r.d_offsets = self.offsets.data_ptr() if self.offsets is not None else None
+        r.d_chars = self.chars.data_ptr() if self.chars is not None else None
+        return r
+
+
+class Context:
+    """One device + one stream (hmj_ctx).  With ``use_torch_stream`` work is issued on torch's
+    current stream so that torch.cuda.Event timing and torch allocations are ordered with it."""
+
+    def __init__(self, device=0, use_torch_stream=True):
+        import torch
+        self._torch = torch
+        self.lib = _lib.load()
+        if not torch.cuda.is_available():
+            raise HmjError(_lib.HMJ_ENODEVICE, "no CUDA device: hashmergejoin_b200 has no CPU path")
+        self.device = torch.device("cuda", device)
+        h = C.c_void_p()
+        if use_torch_stream:
+            with torch.cuda.device(self.device):
+                stream = torch.cuda.current_stream().cuda_stream
+            rc = self.lib.hmj_create_on_stream(C.byref(h), device, C.c_void_p(stream))
+        else:
+            rc = self.lib.hmj_create(C.byref(h), device)
+        if rc != 0:
+            raise HmjError(rc, "hmj_create failed")
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.hmj_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise HmjError(rc, self.lib.hmj_last_error(self.h).decode())
+
+    def _empty(self, n, dtype):
+        return self._torch.empty(int(n), dtype=dtype, device=self.device)
+
+    # ---- A1 hashing
+    def hash_u64(self, keys):
+        _check_dev(keys, 8)
+        out = self._empty(keys.numel(), self._torch.int64)
+        self._ck(self.lib.hmj_hash_u64(self.h, _dptr(keys), keys.numel(), _dptr(out)))
+        return out
+
+    def hash_strings(self, offsets, chars):
+        _check_dev(offsets, 8)
+        n = offsets.numel() - 1
+        out = self._empty(n, self._torch.int64)
+        self._ck(self.lib.hmj_hash_strings(self.h, _dptr(offsets), _dptr(chars), n, _dptr(out)))
+        return out
+
+    # ---- A2-A4 sorting
+    def sort_pairs(self, hash_, rowid=None, out_hash=None, out_rowid=None):
+        _check_dev(hash_, 8)
+        n = hash_.numel()
+        out_hash = out_hash if out_hash is not None else self._empty(n, self._torch.int64)
+        out_rowid = out_rowid if out_rowid is not None else self._empty(n, self._torch.int32)
+        self._ck(self.lib.hmj_sort_pairs(self.h, _dptr(hash_), _dptr(rowid), n, _dptr(out_hash),
+                                         _dptr(out_rowid)))
+        return out_hash, out_rowid
+
+    def hash_sort_u64(self, keys, out_hash=None, out_rowid=None):
+        _check_dev(keys, 8)
+        n = keys.numel()
+        out_hash = out_hash if out_hash is not None else self._empty(n, self._torch.int64)
+        out_rowid = out_rowid if out_rowid is not None else self._empty(n, self._torch.int32)
+        self._ck(self.lib.hmj_hash_sort_u64(self.h, _dptr(keys), n, _dptr(out_hash), _dptr(out_rowid)))
+        return out_hash, out_rowid
+
+    def hash_sort_strings(self, offsets, chars, out_hash=None, out_rowid=None):
+        n = offsets.numel() - 1
+        out_hash = out_hash if out_hash is not None else self._empty(n, self._torch.int64)
+        out_rowid = out_rowid if out_rowid is not None else self._empty(n, self._torch.int32)
+        self._ck(self.lib.hmj_hash_sort_strings(self.h, _dptr(offsets), _dptr(chars), n,
+                                                _dptr(out_hash), _dptr(out_rowid)))
+        return out_hash, out_rowid
+
+    # ---- A5 merge join on sorted relations
+    def merge_join_count(self, R, S):
+        m = C.c_uint64()
+        r, s = R.as_struct(), S.as_struct()
+        self._ck(self.lib.hmj_merge_join_count(self.h, C.byref(r), C.byref(s), C.byref(m)))
+        return m.value
+
+    def merge_join(self, R, S):
+        m = self.merge_join_count(R, S)
+        out_r = self._empty(m, self._torch.int32)
+        out_s = self._empty(m, self._torch.int32)
+        m2 = C.c_uint64()
+        r, s = R.as_struct(), S.as_struct()
+        self._ck(self.lib.hmj_merge_join_write(self.h, C.byref(r), C.byref(s), _dptr(out_r),
+                                               _dptr(out_s), m, C.byref(m2)))
+        assert m2.value == m
+        return out_r, out_s
+
+    def merge_join_aggregate(self, R, S, rvals=None, svals=None):
+        m, sm = C.c_uint64(), C.c_uint64()
+        r, s = R.as_struct(), S.as_struct()
+        self._ck(self.lib.hmj_merge_join_aggregate(self.h, C.byref(r), C.byref(s), _dptr(rvals),
+                                                   _dptr(svals), C.byref(m), C.byref(sm)))
+        return m.value, sm.value
+
+    # ---- whole operator, device inputs
+    def join_u64(self, rkeys, skeys):
+        _check_dev(rkeys, 8)
+        _check_dev(skeys, 8)
+        m = C.c_uint64()
+        self._ck(self.lib.hmj_join_u64(self.h, _dptr(rkeys), rkeys.numel(), _dptr(skeys),
+                                       skeys.numel(), C.byref(m)))
+        return m.value
+
+    def join_strings(self, roff, rchars, soff, schars):
+        m = C.c_uint64()
+        self._ck(self.lib.hmj_join_strings(self.h, _dptr(roff), _dptr(rchars), roff.numel() - 1,
+                                           _dptr(soff), _dptr(schars), soff.numel() - 1, C.byref(m)))
+        return m.value
+
+    def join_result_to_host(self, m):
+        out_r = np.empty(m, dtype=np.uint32)
+        out_s = np.empty(m, dtype=np.uint32)
+        self._ck(self.lib.hmj_join_result_to_host(self.h, _hptr(out_r), _hptr(out_s), m))
+        return out_r, out_s
+
+    # ---- whole operator, host inputs (numpy): the facade / e2e path
+    def join_u64_host(self, rkeys, skeys, out_r=None, out_s=None):
+        m = C.c_uint64()
+        cap = 0 if out_r is None else out_r.size
+        self._ck(self.lib.hmj_join_u64_host(self.h, _hptr(rkeys), rkeys.size, _hptr(skeys), skeys.size,
+                                            _hptr(out_r), _hptr(out_s), cap, C.byref(m)))
+        return m.value
+
+    def join_strings_host(self, roff, rchars, soff, schars, out_r=None, out_s=None):
+        m = C.c_uint64()
+        cap = 0 if out_r is None else out_r.size
+        self._ck(self.lib.hmj_join_strings_host(self.h, _hptr(roff), _hptr(rchars), roff.size - 1,
+                                                _hptr(soff), _hptr(schars), soff.size - 1,
+                                                _hptr(out_r), _hptr(out_s), cap, C.byref(m)))
+        return m.value
+
+    def hash_sort_u64_host(self, keys):
+        n = keys.size
+        h, r = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        self._ck(self.lib.hmj_hash_sort_u64_host(self.h, _hptr(keys), n, _hptr(h), _hptr(r)))
+        return h, r
+
+    def hash_sort_strings_host(self, offsets, chars):
+        n = offsets.size - 1
+        h, r = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        self._ck(self.lib.hmj_hash_sort_strings_host(self.h, _hptr(offsets), _hptr(chars), n,
+                                                     _hptr(h), _hptr(r)))
+        return h, r
+
+    def sort_pairs_host(self, hash_, rowid=None):
+        n = hash_.size
+        h, r = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        self._ck(self.lib.hmj_sort_pairs_host(self.h, _hptr(hash_), _hptr(rowid), n, _hptr(h), _hptr(r)))
+        return h, r
+
+    # ---- A6 partitioning
+    def partition_counts_host(self, hash_, bits):
+        counts = np.zeros(1 << bits, np.uint64)
+        self._ck(self.lib.hmj_partition_counts_host(self.h, _hptr(hash_), hash_.size, bits, _hptr(counts)))
+        return counts
+
+    def partition_pairs(self, hash_, rowid, bits):
+        n = hash_.numel()
+        oh = self._empty(n, self._torch.int64)
+        orow = self._empty(n, self._torch.int32)
+        offs = self._empty((1 << bits) + 1, self._torch.int64)
+        self._ck(self.lib.hmj_partition_pairs(self.h, _dptr(hash_), _dptr(rowid), n, bits, _dptr(oh),
+                                              _dptr(orow), _dptr(offs)))
+        return oh, orow, offs
+
+    # ---- A7 hash-join baseline
+    def hashjoin_build_probe(self, R, S, rvals=None, svals=None):
+        hits, sm = C.c_uint64(), C.c_uint64()
+        r, s = R.as_struct(), S.as_struct()
+        self._ck(self.lib.hmj_hashjoin_build_probe(self.h, C.byref(r), C.byref(s), _dptr(rvals),
+                                                   _dptr(svals), C.byref(hits), C.byref(sm)))
+        return hits.value, sm.value
+
+    # ---- misc
+    def synchronize(self):
+        self._ck(self.lib.hmj_synchronize(self.h))
+
+    def launch_count(self):
+        c = C.c_uint64()
+        self._ck(self.lib.hmj_launch_count(self.h, C.byref(c)))
+        return c.value
+
+    def timings(self):
+        t = Timings()
+        self._ck(self.lib.hmj_get_timings(self.h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in Timings._fields_}
+
+
+def optimal_partition(n):
+    """radix_hash::optimal_partition (radix_hash.h:38-57); host scalar, works without a GPU."""
+    return _lib.load().hmj_optimal_partition(int(n))

@@ -53,6 +53,10 @@ struct hmj_ctx {
   void* pinned = nullptr;  // small pinned host scratch for scalar read-backs
   size_t pinned_bytes = 0;
   uint64_t launches = 0;
+  // decoupled look-back epoch (radix_sort.cu): descriptors carry it so no per-pass memset
+  uint32_t lb_epoch = 0;
+  void* lb_seen_ptr = nullptr;
+  size_t lb_seen_bytes = 0;
   // last whole-operator result
   uint64_t last_pairs = 0;
   hmj_timings tm;

@@ -94,12 +94,6 @@ extern "C" int hmj_launch_count(hmj_ctx* ctx, uint64_t* count) {
   return HMJ_OK;
 }
 
-extern "C" int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out) {
-  if (!ctx || !out) return HMJ_EARG;
-  *out = ctx->tm;
-  return HMJ_OK;
-}
-
 int hmj_ws_get(hmj_ctx* ctx, int slot, size_t bytes, void** out) {
   hmj_buf& b = ctx->ws[slot];
   if (bytes == 0) bytes = 16;

@@ -1,0 +1,119 @@
+// operator.cu -- whole-operator entry points: HashMergeJoin(r_begin,r_end,s_begin,s_end) as one
+// call (hash both relations -> sort both -> merge-join), device- and host-buffer flavours.
+// Stands in for the HashMergeJoin constructor + full iteration (/root/reference hashjoin.h:56-68,
+// 183-195 as driven by hashjoin_bench.cc:126-133) and for radix_non_inplace_par called from
+// host containers (radix_hash.h:351-423).
+#include "common.cuh"
+
+namespace {
+
+enum { EV_START = 0, EV_HASHED, EV_SORTED, EV_JOINED, EV_H2D, EV_D2H };
+
+int sort_side_u64(hmj_ctx* ctx, const uint64_t* d_keys, size_t n, int slot_h, int slot_r,
+                  uint64_t** d_hash, uint32_t** d_rowid) {
+  HMJ_TRY(hmj_ws(ctx, slot_h, n, d_hash));
+  HMJ_TRY(hmj_ws(ctx, slot_r, n, d_rowid));
+  return hmj_hash_sort_u64(ctx, d_keys, n, *d_hash, *d_rowid);
+}
+
+int join_sorted(hmj_ctx* ctx, const hmj_relation* R, const hmj_relation* S, uint64_t* h_num_pairs) {
+  uint64_t m = 0;
+  HMJ_TRY(hmj_merge_join_count(ctx, R, S, &m));
+  uint32_t *out_r = nullptr, *out_s = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_R, (size_t)m, &out_r));
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_S, (size_t)m, &out_s));
+  uint64_t m2 = 0;
+  // TODO(perf): reuse the count pass's tile offsets instead of recounting inside write
+  HMJ_TRY(hmj_merge_join_write(ctx, R, S, out_r, out_s, (size_t)m, &m2));
+  ctx->last_pairs = m2;
+  *h_num_pairs = m2;
+  return HMJ_OK;
+}
+
+}  // namespace
+
+extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
+                            const uint64_t* d_skeys, size_t ns, uint64_t* h_num_pairs) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, h_num_pairs != nullptr);
+  HMJ_ARG(ctx, (nr == 0 || d_rkeys) && (ns == 0 || d_skeys));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->tm.sort_passes = 0;
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));  // identity hash: no kernel
+  hmj_relation R = {}, S = {};
+  uint64_t* h = nullptr;
+  uint32_t* rid = nullptr;
+  HMJ_TRY(sort_side_u64(ctx, d_rkeys, nr, WS_R_HASH, WS_R_ROWID, &h, &rid));
+  R.d_hash = h; R.d_rowid = rid; R.n = nr; R.key_kind = HMJ_KEY_U64;
+  HMJ_TRY(sort_side_u64(ctx, d_skeys, ns, WS_S_HASH, WS_S_ROWID, &h, &rid));
+  S.d_hash = h; S.d_rowid = rid; S.n = ns; S.key_kind = HMJ_KEY_U64;
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
+  HMJ_TRY(join_sorted(ctx, &R, &S, h_num_pairs));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
+                                size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars,
+                                size_t ns, uint64_t* h_num_pairs) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, h_num_pairs != nullptr);
+  HMJ_ARG(ctx, (nr == 0 || d_roffsets) && (ns == 0 || d_soffsets));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->tm.sort_passes = 0;
+  uint64_t *rh = nullptr, *sh = nullptr;
+  uint32_t *rr = nullptr, *sr = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_R_HASH, nr, &rh));
+  HMJ_TRY(hmj_ws(ctx, WS_R_ROWID, nr, &rr));
+  HMJ_TRY(hmj_ws(ctx, WS_S_HASH, ns, &sh));
+  HMJ_TRY(hmj_ws(ctx, WS_S_ROWID, ns, &sr));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  HMJ_TRY(hmj_hash_strings(ctx, d_roffsets, d_rchars, nr, rh));
+  HMJ_TRY(hmj_hash_strings(ctx, d_soffsets, d_schars, ns, sh));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
+  HMJ_TRY(hmj_sort_pairs(ctx, rh, nullptr, nr, rh, rr));
+  HMJ_TRY(hmj_sort_pairs(ctx, sh, nullptr, ns, sh, sr));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
+  hmj_relation R = {rh, rr, nr, HMJ_KEY_STRING, d_roffsets, d_rchars};
+  hmj_relation S = {sh, sr, ns, HMJ_KEY_STRING, d_soffsets, d_schars};
+  HMJ_TRY(join_sorted(ctx, &R, &S, h_num_pairs));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_join_result(hmj_ctx* ctx, const uint32_t** d_out_r, const uint32_t** d_out_s,
+                               uint64_t* num_pairs) {
+  if (!ctx) return HMJ_EARG;
+  if (d_out_r) *d_out_r = reinterpret_cast<const uint32_t*>(ctx->ws[WS_OUT_R].ptr);
+  if (d_out_s) *d_out_s = reinterpret_cast<const uint32_t*>(ctx->ws[WS_OUT_S].ptr);
+  if (num_pairs) *num_pairs = ctx->last_pairs;
+  return HMJ_OK;
+}
+
+extern "C" int hmj_join_result_to_host(hmj_ctx* ctx, uint32_t* h_out_r, uint32_t* h_out_s,
+                                       size_t cap) {
+  if (!ctx) return HMJ_EARG;
+  const size_t m = (size_t)ctx->last_pairs;
+  if (m > cap) return hmj_fail(ctx, HMJ_ECAPACITY, "output capacity too small", __FILE__, __LINE__);
+  if (m == 0) return HMJ_OK;
+  HMJ_ARG(ctx, h_out_r && h_out_s);
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_r, ctx->ws[WS_OUT_R].ptr, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_s, ctx->ws[WS_OUT_S].ptr, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out) {
+  if (!ctx || !out) return HMJ_EARG;
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  hmj_timings t = ctx->tm;
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_HASHED]) == cudaSuccess) t.hash_ms = ms;
+  if (cudaEventElapsedTime(&ms, ctx->ev[EV_HASHED], ctx->ev[EV_SORTED]) == cudaSuccess) t.sort_ms = ms;
+  if (cudaEventElapsedTime(&ms, ctx->ev[EV_SORTED], ctx->ev[EV_JOINED]) == cudaSuccess) t.join_ms = ms;
+  if (cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_JOINED]) == cudaSuccess) t.total_ms = ms;
+  cudaGetLastError();  // events never recorded yet: not an error for the caller
+  *out = t;
+  return HMJ_OK;
+}

@@ -1,0 +1,530 @@
+// radix_sort.cu -- K2 + K3: onesweep-style LSD radix sort of (u64 hash, u32 row-id) pairs.
+//
+// Stands in for the reference's MSD radix sort of (hash,key,value) tuples:
+//   radix_non_inplace_par  radix_hash.h:351-423 (worker :294-346, recursion :122-292)
+//   radix_inplace_seq/par  radix_hash.h:425-654
+//   radix_int_inplace / radix_int_non_inplace  radix_sort.h:333-398,452-522
+// The reference result that is pinned by its tests is "hash column fully ascending"; order
+// inside an equal-hash run is unspecified there.  This sort is STABLE, so equal hashes come out
+// in ascending input order, which makes the output canonical.
+//
+// Structure (all SoA, HBM resident):
+//   K2  radix_histogram_kernel : one read of the key column -> 8 x 256 digit histograms
+//   K2b radix_scan_kernel      : exclusive scan per digit -> global bin offsets, skip flags
+//   K3  onesweep_pass_kernel   : per pass, one read + one write of the pairs.  Tiles are taken
+//       from a dynamic counter; digits are ranked inside each warp with __match_any_sync
+//       (warp-private shared-memory histograms), tile prefixes come from a decoupled look-back
+//       chain over single-word (flag|epoch|count) descriptors; keys and row ids are staged in
+//       shared memory in tile-sorted order so every digit bin is written as a contiguous run.
+// Algorithmic bytes per pair: histogram 8; each executed pass 12 read + 12 written (the first
+// pass of an iota-row-id sort reads 8).
+#include "common.cuh"
+
+namespace {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int NUM_PASSES = 64 / RADIX_BITS;
+
+// ---------------------------------------------------------------- K2: histogram
+constexpr int HIST_THREADS = 512;
+constexpr int HIST_ITEMS = 8;  // keys per thread per iteration
+
+__global__ void __launch_bounds__(HIST_THREADS)
+radix_histogram_kernel(const uint64_t* __restrict__ keys, size_t n, uint32_t* __restrict__ g_hist) {
+  __shared__ uint32_t s_hist[NUM_PASSES][RADIX];
+  for (int i = threadIdx.x; i < NUM_PASSES * RADIX; i += HIST_THREADS) (&s_hist[0][0])[i] = 0;
+  __syncthreads();
+  const size_t chunk = (size_t)HIST_THREADS * HIST_ITEMS;
+  for (size_t base = (size_t)blockIdx.x * chunk; base < n; base += (size_t)gridDim.x * chunk) {
+    uint64_t k[HIST_ITEMS];
+#pragma unroll
+    for (int j = 0; j < HIST_ITEMS; ++j) {
+      const size_t i = base + (size_t)j * HIST_THREADS + threadIdx.x;
+      k[j] = i < n ? __ldcs(keys + i) : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < HIST_ITEMS; ++j) {
+      const size_t i = base + (size_t)j * HIST_THREADS + threadIdx.x;
+      if (i < n) {
+#pragma unroll
+        for (int p = 0; p < NUM_PASSES; ++p)
+          atomicAdd(&s_hist[p][(k[j] >> (p * RADIX_BITS)) & (RADIX - 1)], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < NUM_PASSES * RADIX; i += HIST_THREADS) {
+    const uint32_t c = (&s_hist[0][0])[i];
+    if (c) atomicAdd(g_hist + i, c);
+  }
+}
+
+// One block per digit position: exclusive scan of its 256 bins (in place) and a flag telling
+// whether the pass is trivial (one bin holds every key).
+__global__ void __launch_bounds__(RADIX)
+radix_scan_kernel(uint32_t* __restrict__ g_hist, uint32_t n32, uint32_t* __restrict__ g_skip) {
+  __shared__ uint32_t s_warp[RADIX / 32];
+  const int p = blockIdx.x, d = threadIdx.x, lane = d & 31, w = d >> 5;
+  const uint32_t c = g_hist[p * RADIX + d];
+  uint32_t x = c;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
+  }
+  if (lane == 31) s_warp[w] = x;
+  const int trivial = __syncthreads_or(c == n32);
+  uint32_t pre = 0;
+  for (int i = 0; i < w; ++i) pre += s_warp[i];
+  g_hist[p * RADIX + d] = pre + x - c;
+  if (d == 0) g_skip[p] = trivial ? 1u : 0u;
+}
+
+// ---------------------------------------------------------------- K3: onesweep pass
+// Look-back descriptor: one 64-bit word = status(2) | epoch(16) | count(46).  The epoch makes
+// descriptors of earlier passes/sorts read as "not ready", so the chain needs no memset.
+constexpr uint64_t LB_PARTIAL = 1ull << 62;
+constexpr uint64_t LB_INCLUSIVE = 2ull << 62;
+constexpr uint64_t LB_STATUS_MASK = 3ull << 62;
+constexpr int LB_EPOCH_SHIFT = 46;
+constexpr uint64_t LB_EPOCH_MASK = 0xFFFFull << LB_EPOCH_SHIFT;
+constexpr uint64_t LB_VALUE_MASK = (1ull << LB_EPOCH_SHIFT) - 1;
+
+__device__ __forceinline__ void lb_store(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t lb_load(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS = 1>
+struct OnesweepCfg {
+  static constexpr int WARPS = THREADS / 32;
+  static constexpr int TILE = THREADS * ITEMS;
+  static constexpr size_t SMEM_BYTES =
+      (size_t)TILE * 8 + (size_t)TILE * 4 + (size_t)WARPS * RADIX * 4 + 3 * RADIX * 4 + 64;
+};
+
+// keys_in/vals_in -> keys_out/vals_out, stable on digit (key >> shift) & 255.
+// vals_in == nullptr means the payload is the element's global index (row id iota).
+template <int THREADS, int ITEMS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
+                     uint32_t n, int shift, const uint32_t* __restrict__ bin_offsets,
+                     uint64_t* __restrict__ lookback, uint32_t* __restrict__ tile_counter,
+                     uint32_t epoch) {
+  using Cfg = OnesweepCfg<THREADS, ITEMS>;
+  constexpr int WARPS = Cfg::WARPS;
+  constexpr int TILE = Cfg::TILE;
+  static_assert(THREADS >= RADIX, "one thread per digit is needed for the look-back");
+
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + TILE);
+  uint32_t* s_whist = s_vals + TILE;             // [WARPS][RADIX] warp-private counts/offsets
+  uint32_t* s_tile_off = s_whist + WARPS * RADIX;  // [RADIX] start of digit inside the tile
+  uint32_t* s_gbase = s_tile_off + RADIX;          // [RADIX] global start of digit minus tile_off
+  uint32_t* s_scan = s_gbase + RADIX;              // [RADIX/32] + tile id
+  uint32_t* s_tile_id = s_scan + RADIX / 32 + 1;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  if (tid == 0) *s_tile_id = atomicAdd(tile_counter, 1u);
+  for (int i = tid; i < WARPS * RADIX; i += THREADS) s_whist[i] = 0;
+  __syncthreads();
+  const uint32_t tile = *s_tile_id;
+  const uint32_t tile_base = tile * (uint32_t)TILE;
+  const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+
+  // ---- load keys, warp-striped: item k of lane l sits at warp_base + k*32 + l
+  const uint32_t warp_base = tile_base + warp * (32 * ITEMS);
+  uint64_t key[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const uint32_t idx = warp_base + k * 32 + lane;
+    key[k] = (idx < n) ? __ldcs(keys_in + idx) : ~0ull;
+  }
+
+  // ---- rank digits inside the warp (stable in item order k, lane)
+  uint32_t* whist = s_whist + warp * RADIX;
+  uint16_t rank[ITEMS];
+  const uint32_t lt_mask = (1u << lane) - 1;
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if (lane == leader) {
+      old = whist[d];
+      whist[d] = old + __popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rank[k] = (uint16_t)(old + __popc(peers & lt_mask));
+    __syncwarp();
+  }
+  __syncthreads();
+
+  // ---- per digit: exclusive offsets over warps, tile totals, scan over digits, look-back
+  uint32_t count = 0;
+  if (tid < RADIX) {
+    uint32_t sum = 0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) {
+      const uint32_t c = s_whist[w * RADIX + tid];
+      s_whist[w * RADIX + tid] = sum;
+      sum += c;
+    }
+    count = sum;
+    // out-of-range items were given digit 255 and rank last inside it; they are not data.
+    uint32_t pub = count;
+    if (tid == RADIX - 1) pub -= (uint32_t)TILE - valid;
+    uint64_t* my_desc = lookback + (size_t)tile * RADIX + tid;
+    const uint64_t tag = (uint64_t)epoch << LB_EPOCH_SHIFT;
+    if (tile != 0) lb_store(my_desc, LB_PARTIAL | tag | pub);
+    // inclusive scan of tile counts across the 256 digits
+    uint32_t x = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_scan[warp] = x;
+    // (only warps 0..7 are in this branch; they synchronise on a named barrier)
+    asm volatile("bar.sync 1, %0;" ::"n"(RADIX));
+    uint32_t pre = 0;
+    for (int i = 0; i < warp; ++i) pre += s_scan[i];
+    const uint32_t tile_off = pre + x - count;
+    s_tile_off[tid] = tile_off;
+    // decoupled look-back over earlier tiles of this digit
+    uint32_t excl = 0;
+    if (tile != 0) {
+      int64_t prev = (int64_t)tile - 1;
+      while (true) {
+        const uint64_t v = lb_load(lookback + (size_t)prev * RADIX + tid);
+        if ((v & LB_EPOCH_MASK) != tag || (v & LB_STATUS_MASK) == 0) continue;  // not ready
+        excl += (uint32_t)(v & LB_VALUE_MASK);
+        if ((v & LB_STATUS_MASK) == LB_INCLUSIVE) break;
+        --prev;
+      }
+    }
+    lb_store(my_desc, LB_INCLUSIVE | tag | (uint64_t)(excl + pub));
+    s_gbase[tid] = bin_offsets[tid] + excl - tile_off;
+  }
+  __syncthreads();
+
+  // ---- scatter keys into tile-sorted order in shared memory
+  uint16_t pos[ITEMS];
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
+    const uint32_t p = s_tile_off[d] + whist[d] + rank[k];
+    pos[k] = (uint16_t)p;
+    s_keys[p] = key[k];
+  }
+  // payloads (loaded late to keep registers low)
+#pragma unroll
+  for (int k = 0; k < ITEMS; ++k) {
+    const uint32_t idx = warp_base + k * 32 + lane;
+    uint32_t v = idx;
+    if (vals_in != nullptr && idx < n) v = __ldcs(vals_in + idx);
+    s_vals[pos[k]] = v;
+  }
+  __syncthreads();
+
+  // ---- write out: consecutive threads write consecutive slots of a digit's run
+#pragma unroll 4
+  for (uint32_t i = tid; i < valid; i += THREADS) {
+    const uint64_t kk = s_keys[i];
+    const uint32_t d = (uint32_t)(kk >> shift) & (RADIX - 1);
+    const uint32_t dst = s_gbase[d] + i;
+    keys_out[dst] = kk;
+    vals_out[dst] = s_vals[i];
+  }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------- host driver
+namespace {
+
+__global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n) {
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = i;
+}
+
+template <int THREADS, int ITEMS, int MIN_BLOCKS>
+int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
+                uint32_t* vout, uint32_t n, int shift, const uint32_t* bins, uint64_t* lookback,
+                uint32_t* counter, uint32_t epoch) {
+  using Cfg = OnesweepCfg<THREADS, ITEMS>;
+  // per-device attribute; cheap enough to set on every launch
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)Cfg::SMEM_BYTES));
+  const uint32_t tiles = (uint32_t)hmj_div_up(n, Cfg::TILE);
+  onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
+      kin, vin, kout, vout, n, shift, bins, lookback, counter, epoch);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
+}
+
+int sort_cfg_from_env() {
+  static int cfg = -1;
+  if (cfg < 0) {
+    const char* e = getenv("HMJ_SORT_CFG");
+    cfg = e ? atoi(e) : 0;
+  }
+  return cfg;
+}
+
+int tile_items_for_cfg(int cfg) {
+  switch (cfg) {
+    case 1: return OnesweepCfg<512, 8>::TILE;
+    case 2: return OnesweepCfg<256, 24>::TILE;
+    case 3: return OnesweepCfg<384, 16>::TILE;
+    case 4: return OnesweepCfg<512, 16>::TILE;
+    default: return OnesweepCfg<256, 16>::TILE;
+  }
+}
+
+}  // namespace
+
+int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in, size_t n,
+                  uint64_t* keys_out, uint32_t* vals_out) {
+  HMJ_ARG(ctx, n < (size_t(1) << 32) - (size_t(1) << 16));
+  if (n == 0) return HMJ_OK;
+  HMJ_ARG(ctx, keys_in && keys_out && vals_out);
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const uint32_t n32 = (uint32_t)n;
+  const int cfg = sort_cfg_from_env();
+  const int tile_items = tile_items_for_cfg(cfg);
+  const size_t tiles = hmj_div_up(n, tile_items);
+
+  // scratch: [8*256 bins][8 skip flags][8 tile counters]
+  uint32_t* d_hist = nullptr;
+  const size_t hist_words = NUM_PASSES * RADIX + 2 * NUM_PASSES;
+  HMJ_TRY(hmj_ws(ctx, WS_HIST, hist_words, &d_hist));
+  uint32_t* d_skip = d_hist + NUM_PASSES * RADIX;
+  uint32_t* d_counters = d_skip + NUM_PASSES;
+  HMJ_CUDA(ctx, cudaMemsetAsync(d_hist, 0, hist_words * sizeof(uint32_t), st));
+
+  const size_t chunk = (size_t)HIST_THREADS * HIST_ITEMS;
+  const int hgrid = (int)min(hmj_div_up(n, chunk), (size_t)ctx->num_sms * 4);
+  radix_histogram_kernel<<<hgrid, HIST_THREADS, 0, st>>>(keys_in, n, d_hist);
+  HMJ_LAUNCHED(ctx);
+  radix_scan_kernel<<<NUM_PASSES, RADIX, 0, st>>>(d_hist, n32, d_skip);
+  HMJ_LAUNCHED(ctx);
+
+  // Trivial passes (all keys share the digit) are skipped when the relation is large enough
+  // for a pass to cost more than the read-back of 8 flags.
+  bool skip[NUM_PASSES] = {};
+  if (n >= (size_t(1) << 21)) {
+    uint32_t* h_skip = reinterpret_cast<uint32_t*>(ctx->pinned);
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h_skip, d_skip, NUM_PASSES * sizeof(uint32_t),
+                                  cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+    for (int p = 0; p < NUM_PASSES; ++p) skip[p] = h_skip[p] != 0;
+  }
+  int P = 0;
+  for (int p = 0; p < NUM_PASSES; ++p) P += skip[p] ? 0 : 1;
+  ctx->tm.sort_passes += (uint32_t)P;
+
+  const bool aliased = (keys_in == keys_out) || (vals_in != nullptr && vals_in == vals_out);
+  if (P == 0) {
+    if (keys_in != keys_out)
+      HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
+    if (vals_in == nullptr) {
+      iota_kernel<<<(int)min(hmj_div_up(n, 256), (size_t)ctx->num_sms * 8), 256, 0, st>>>(vals_out, n32);
+      HMJ_LAUNCHED(ctx);
+    } else if (vals_in != vals_out) {
+      HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, vals_in, n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    return HMJ_OK;
+  }
+
+  uint64_t* tmp_k = nullptr;
+  uint32_t* tmp_v = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, n, &tmp_k));
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, n, &tmp_v));
+
+  // look-back descriptors: tiles x 256 words, reused by every pass thanks to the epoch tag
+  uint64_t* d_lb = nullptr;
+  const size_t lb_words = tiles * RADIX;
+  HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, lb_words, &d_lb));
+  if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
+      ctx->lb_epoch + NUM_PASSES >= 0xFFFF) {
+    HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
+    ctx->lb_seen_ptr = d_lb;
+    ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
+    ctx->lb_epoch = 0;
+  }
+
+  const bool end_in_tmp = aliased && (P & 1);
+  const uint64_t* cur_k = keys_in;
+  const uint32_t* cur_v = vals_in;
+  int j = 0;
+  for (int p = 0; p < NUM_PASSES; ++p) {
+    if (skip[p]) continue;
+    bool to_out = end_in_tmp ? (j & 1) : (((P - 1 - j) & 1) == 0);
+    uint64_t* dk = to_out ? keys_out : tmp_k;
+    uint32_t* dv = to_out ? vals_out : tmp_v;
+    const uint32_t epoch = ++ctx->lb_epoch;
+    const uint32_t* bins = d_hist + p * RADIX;
+    int rc;
+    switch (cfg) {
+      case 1: rc = launch_pass<512, 8, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+      case 2: rc = launch_pass<256, 24, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+      case 3: rc = launch_pass<384, 16, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+      case 4: rc = launch_pass<512, 16, 1>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+      default: rc = launch_pass<256, 16, 3>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+    }
+    HMJ_TRY(rc);
+    cur_k = dk;
+    cur_v = dv;
+    ++j;
+  }
+  if (end_in_tmp) {
+    HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, tmp_k, n * 8, cudaMemcpyDeviceToDevice, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, tmp_v, n * 4, cudaMemcpyDeviceToDevice, st));
+  }
+  return HMJ_OK;
+}
+
+extern "C" int hmj_sort_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid,
+                              size_t n, uint64_t* d_hash_out, uint32_t* d_rowid_out) {
+  if (!ctx) return HMJ_EARG;
+  return hmj_impl_sort(ctx, d_hash, d_rowid, n, d_hash_out, d_rowid_out);
+}
+
+extern "C" int hmj_sort_int_pairs(hmj_ctx* ctx, const uint64_t* d_keys, const uint32_t* d_vals,
+                                  size_t n, uint64_t* d_keys_out, uint32_t* d_vals_out) {
+  if (!ctx) return HMJ_EARG;
+  return hmj_impl_sort(ctx, d_keys, d_vals, n, d_keys_out, d_vals_out);
+}
+
+extern "C" int hmj_hash_sort_u64(hmj_ctx* ctx, const uint64_t* d_keys, size_t n,
+                                 uint64_t* d_hash_out, uint32_t* d_rowid_out) {
+  if (!ctx) return HMJ_EARG;
+  // std::hash<integral> is the identity: the key column IS the hash column, and the first
+  // scatter pass generates the row ids, so no separate hash kernel runs.
+  return hmj_impl_sort(ctx, d_keys, nullptr, n, d_hash_out, d_rowid_out);
+}
+
+extern "C" int hmj_hash_sort_strings(hmj_ctx* ctx, const uint64_t* d_offsets,
+                                     const uint8_t* d_chars, size_t n, uint64_t* d_hash_out,
+                                     uint32_t* d_rowid_out) {
+  if (!ctx) return HMJ_EARG;
+  if (n == 0) return HMJ_OK;
+  // hash into the output column, then sort it in place (ping-pong through the workspace)
+  HMJ_TRY(hmj_hash_strings(ctx, d_offsets, d_chars, n, d_hash_out));
+  return hmj_impl_sort(ctx, d_hash_out, nullptr, n, d_hash_out, d_rowid_out);
+}
+
+// ---------------------------------------------------------------- K8: top-bits partition
+// Stands in for partition_only's counting loop and scatter (/root/reference
+// partitioned_hash.h:57-60,75-79): partition p = hash >> (64 - bits).  The scatter reuses the
+// onesweep pass with the digit taken from the top bits, so a partition is written as one
+// contiguous, stable run (the reference's push_back order under a mutex is nondeterministic).
+namespace {
+
+constexpr int PART_THREADS = 512;
+
+// counts[p] += 1 for p = key >> shift; shared-memory bins when they fit (bits <= 12)
+template <typename CountT>
+__global__ void __launch_bounds__(PART_THREADS)
+partition_count_kernel(const uint64_t* __restrict__ keys, size_t n, int shift, int bins,
+                       CountT* __restrict__ g_counts, int use_smem) {
+  extern __shared__ uint32_t s_bins[];
+  if (use_smem) {
+    for (int i = threadIdx.x; i < bins; i += PART_THREADS) s_bins[i] = 0;
+    __syncthreads();
+  }
+  const size_t stride = (size_t)gridDim.x * PART_THREADS;
+  for (size_t i = (size_t)blockIdx.x * PART_THREADS + threadIdx.x; i < n; i += stride) {
+    const uint32_t p = (uint32_t)(__ldcs(keys + i) >> shift);
+    if (use_smem) atomicAdd(&s_bins[p], 1u);
+    else atomicAdd(g_counts + p, (CountT)1);
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < bins; i += PART_THREADS) {
+      const uint32_t c = s_bins[i];
+      if (c) atomicAdd(g_counts + i, (CountT)c);
+    }
+  }
+}
+
+__global__ void partition_offsets_kernel(const uint32_t* __restrict__ excl, int bins, uint32_t n,
+                                         uint64_t* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < bins) out[i] = excl[i];
+  if (i == bins) out[i] = n;
+}
+
+}  // namespace
+
+extern "C" int hmj_partition_counts(hmj_ctx* ctx, const uint64_t* d_hash, size_t n, int bits,
+                                    uint64_t* d_counts) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, bits >= 1 && bits <= 16 && d_counts && (n == 0 || d_hash));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int bins = 1 << bits;
+  HMJ_CUDA(ctx, cudaMemsetAsync(d_counts, 0, (size_t)bins * 8, ctx->stream));
+  if (n == 0) return HMJ_OK;
+  const int use_smem = bits <= 12;
+  const int grid = (int)min(hmj_div_up(n, PART_THREADS * 8), (size_t)ctx->num_sms * 4);
+  partition_count_kernel<unsigned long long><<<grid, PART_THREADS, use_smem ? bins * 4 : 0, ctx->stream>>>(
+      d_hash, n, 64 - bits, bins, reinterpret_cast<unsigned long long*>(d_counts), use_smem);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
+}
+
+extern "C" int hmj_partition_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid,
+                                   size_t n, int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
+                                   uint64_t* d_part_offsets) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, bits >= 1 && bits <= 8 && d_part_offsets);
+  HMJ_ARG(ctx, n < (size_t(1) << 32) - (size_t(1) << 16));
+  HMJ_ARG(ctx, n == 0 || (d_hash && d_hash_out && d_rowid_out));
+  HMJ_ARG(ctx, d_hash != d_hash_out && (d_rowid == nullptr || d_rowid != d_rowid_out));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int bins = 1 << bits;
+  const uint32_t n32 = (uint32_t)n;
+  uint32_t* d_hist = nullptr;
+  const size_t hist_words = NUM_PASSES * RADIX + 2 * NUM_PASSES;
+  HMJ_TRY(hmj_ws(ctx, WS_HIST, hist_words, &d_hist));
+  uint32_t* d_skip = d_hist + NUM_PASSES * RADIX;
+  uint32_t* d_counters = d_skip + NUM_PASSES;
+  HMJ_CUDA(ctx, cudaMemsetAsync(d_hist, 0, hist_words * sizeof(uint32_t), st));
+  if (n) {
+    const int grid = (int)min(hmj_div_up(n, PART_THREADS * 8), (size_t)ctx->num_sms * 4);
+    partition_count_kernel<uint32_t><<<grid, PART_THREADS, RADIX * 4, st>>>(d_hash, n, 64 - bits, RADIX, d_hist, 1);
+    HMJ_LAUNCHED(ctx);
+  }
+  radix_scan_kernel<<<1, RADIX, 0, st>>>(d_hist, n32, d_skip);
+  HMJ_LAUNCHED(ctx);
+  partition_offsets_kernel<<<(bins + 1 + 255) / 256, 256, 0, st>>>(d_hist, bins, n32, d_part_offsets);
+  HMJ_LAUNCHED(ctx);
+  if (n == 0) return HMJ_OK;
+  const int tile_items = tile_items_for_cfg(0);
+  const size_t tiles = hmj_div_up(n, tile_items);
+  uint64_t* d_lb = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, tiles * RADIX, &d_lb));
+  if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
+      ctx->lb_epoch + NUM_PASSES >= 0xFFFF) {
+    HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
+    ctx->lb_seen_ptr = d_lb;
+    ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
+    ctx->lb_epoch = 0;
+  }
+  const uint32_t epoch = ++ctx->lb_epoch;
+  return launch_pass<256, 16, 3>(ctx, d_hash, d_rowid, d_hash_out, d_rowid_out, n32, 64 - bits,
+                                 d_hist, d_lb, d_counters, epoch);
+}

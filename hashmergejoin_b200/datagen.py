@@ -1,0 +1,136 @@
+"""Seeded synthetic relations for tests and benchmarks (harness code, not part of the hot path).
+
+* ``strgen``  -- relations shaped like the reference's ``create_strvec`` (/root/reference
+  strgen.cc:28-61): the first q = ceil(sqrt(n)) rows are base words, the rest are
+  ``word_i + "-" + word_j`` row-major until n rows, then shuffled.  The reference reads
+  /usr/share/dict/words, which does not exist in this image, so base words come from a seeded
+  synthetic list of unique lowercase words (lengths 3..14, mean ~8.5, row mean ~18 bytes).
+* ``unique_u64`` -- n distinct uniform-looking 64-bit keys (splitmix64 finaliser of 0..n-1,
+  which is a bijection on 64 bits), and ``permuted`` -- a seeded permutation of a relation.
+Columnar layout: offsets u64[n+1] + chars u8[] for strings, u64[n] for integers.
+"""
+import math
+
+import numpy as np
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def splitmix64(x):
+    """Bijective 64-bit mix (numpy uint64, wrapping arithmetic)."""
+    x = np.asarray(x, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        x = x ^ (x >> np.uint64(31))
+    return x
+
+
+def unique_u64(n, seed=0):
+    """n distinct 64-bit keys."""
+    base = np.arange(n, dtype=np.uint64) + (np.uint64(seed) << np.uint64(40))
+    return splitmix64(base)
+
+
+def permuted(arr, seed):
+    rng = np.random.default_rng(seed)
+    return arr[rng.permutation(arr.shape[0])]
+
+
+def word_list(q, seed=1234):
+    """q unique lowercase words of length 3..14 as (offsets u64[q+1], chars u8[])."""
+    rng = np.random.default_rng(seed)
+    words = set()
+    out = []
+    while len(out) < q:
+        need = q - len(out)
+        lens = rng.integers(3, 15, size=need * 2)
+        for ln in lens:
+            w = bytes(rng.integers(97, 123, size=int(ln), dtype=np.uint8))
+            if w not in words:
+                words.add(w)
+                out.append(w)
+                if len(out) == q:
+                    break
+    lens = np.array([len(w) for w in out], dtype=np.uint64)
+    offsets = np.zeros(q + 1, dtype=np.uint64)
+    np.cumsum(lens, out=offsets[1:])
+    chars = np.frombuffer(b"".join(out), dtype=np.uint8).copy()
+    return offsets, chars
+
+
+def strgen_unshuffled(n, seed=1234):
+    """create_strvec(n) before the shuffle: (offsets, chars, values)."""
+    q = int(math.ceil(math.sqrt(n)))
+    woff, wchars = word_list(q, seed)
+    wlen = (woff[1:] - woff[:-1]).astype(np.int64)
+    nbase = min(q, n)
+    npairs = n - nbase
+    # row r >= q is pair (i, j) = divmod(r - q, q)
+    pi = np.arange(npairs, dtype=np.int64) // q
+    pj = np.arange(npairs, dtype=np.int64) % q
+    lens = np.concatenate([wlen[:nbase], wlen[pi] + 1 + wlen[pj]]).astype(np.uint64)
+    offsets = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum(lens, out=offsets[1:])
+    chars = np.empty(int(offsets[-1]), dtype=np.uint8)
+    # base words
+    chars[: int(offsets[nbase])] = wchars[: int(woff[nbase])]
+    # pairs, filled by (vectorised) per-length-class gathers
+    if npairs:
+        start = offsets[nbase:-1].astype(np.int64)
+        li, lj = wlen[pi], wlen[pj]
+        wo = woff[:-1].astype(np.int64)
+        for k in range(int(wlen.max())):
+            sel = li > k
+            chars[start[sel] + k] = wchars[wo[pi[sel]] + k]
+            sel = lj > k
+            chars[start[sel] + li[sel] + 1 + k] = wchars[wo[pj[sel]] + k]
+        chars[start + li] = ord("-")
+    values = np.concatenate([np.arange(nbase, dtype=np.uint64), (pi + pj).astype(np.uint64)])
+    return offsets, chars, values
+
+
+def take_rows(offsets, chars, order):
+    """Reorders a string column: row k of the result is row order[k] of the input."""
+    lens = (offsets[1:] - offsets[:-1])[order]
+    new_off = np.zeros(order.shape[0] + 1, dtype=np.uint64)
+    np.cumsum(lens, out=new_off[1:])
+    src_start = offsets[:-1][order].astype(np.int64)
+    # index of every output byte: repeat starts and add intra-row position
+    total = int(new_off[-1])
+    row_of_byte = np.repeat(np.arange(order.shape[0], dtype=np.int64), lens.astype(np.int64))
+    pos = np.arange(total, dtype=np.int64) - new_off[:-1].astype(np.int64)[row_of_byte]
+    new_chars = chars[src_start[row_of_byte] + pos]
+    return new_off, new_chars
+
+
+def strgen(n, seed=1234, shuffle_seed=1):
+    """create_strvec(n): unique keys, shuffled with a seeded permutation.
+    Returns (offsets, chars, values, order) where order[k] = unshuffled row of output row k."""
+    offsets, chars, values = strgen_unshuffled(n, seed)
+    order = np.random.default_rng(shuffle_seed).permutation(n)
+    new_off, new_chars = take_rows(offsets, chars, order)
+    return new_off, new_chars, values[order], order
+
+
+def strings_from_list(items):
+    """Python list of bytes/str -> (offsets, chars)."""
+    bs = [s.encode() if isinstance(s, str) else bytes(s) for s in items]
+    offsets = np.zeros(len(bs) + 1, dtype=np.uint64)
+    if bs:
+        np.cumsum(np.array([len(b) for b in bs], dtype=np.uint64), out=offsets[1:])
+    chars = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, np.uint8)
+    if chars.size == 0:
+        chars = np.zeros(1, np.uint8)[:0].copy()
+    return offsets, chars
+
+
+def zipf_indices(n_draws, n_keys, s=1.0, seed=7):
+    """n_draws ranks in [0,n_keys) with P(k) ~ 1/(k+1)^s via a seeded inverse CDF."""
+    rng = np.random.default_rng(seed)
+    w = 1.0 / np.power(np.arange(1, n_keys + 1, dtype=np.float64), s)
+    cdf = np.cumsum(w)
+    cdf /= cdf[-1]
+    u = rng.random(n_draws)
+    return np.minimum(np.searchsorted(cdf, u), n_keys - 1).astype(np.int64)
