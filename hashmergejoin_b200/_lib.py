@@ -40,6 +40,7 @@ class Timings(C.Structure):
         ("hash_ms", C.c_float), ("histogram_ms", C.c_float), ("sort_ms", C.c_float),
         ("join_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
         ("total_ms", C.c_float), ("sort_passes", C.c_uint32),
+        ("pass_ms_sum", C.c_float), ("pass_launches", C.c_uint32),
     ]
 
 
@@ -78,6 +79,8 @@ SIGNATURES = {
     "hmj_sort_pairs_host": (_I, [_P, _P, _P, _SZ, _P, _P]),
     "hmj_partition_counts": (_I, [_P, _P, _SZ, _I, _P]),
     "hmj_partition_pairs": (_I, [_P, _P, _P, _SZ, _I, _P, _P, _P]),
+    "hmj_partition_pairs_base": (_I, [_P, _P, _P, C.c_uint32, _SZ, _I, _P, _P, _P]),
+    "hmj_set_profiling": (_I, [_P, _I]),
     "hmj_partition_counts_host": (_I, [_P, _P, _SZ, _I, _P]),
     "hmj_hashjoin_build_probe": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),
     "hmj_get_timings": (_I, [_P, C.POINTER(Timings)]),

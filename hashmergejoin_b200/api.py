@@ -209,13 +209,14 @@ class Context:
         self._ck(self.lib.hmj_partition_counts_host(self.h, _hptr(hash_), hash_.size, bits, _hptr(counts)))
         return counts
 
-    def partition_pairs(self, hash_, rowid, bits):
+    def partition_pairs(self, hash_, rowid, bits, rowid_base=0, out=None):
         n = hash_.numel()
-        oh = self._empty(n, self._torch.int64)
-        orow = self._empty(n, self._torch.int32)
-        offs = self._empty((1 << bits) + 1, self._torch.int64)
-        self._ck(self.lib.hmj_partition_pairs(self.h, _dptr(hash_), _dptr(rowid), n, bits, _dptr(oh),
-                                              _dptr(orow), _dptr(offs)))
+        if out is None:
+            out = (self._empty(n, self._torch.int64), self._empty(n, self._torch.int32),
+                   self._empty((1 << bits) + 1, self._torch.int64))
+        oh, orow, offs = out
+        self._ck(self.lib.hmj_partition_pairs_base(self.h, _dptr(hash_), _dptr(rowid), rowid_base, n,
+                                                   bits, _dptr(oh), _dptr(orow), _dptr(offs)))
         return oh, orow, offs
 
     # ---- A7 hash-join baseline
@@ -234,6 +235,9 @@ class Context:
         c = C.c_uint64()
         self._ck(self.lib.hmj_launch_count(self.h, C.byref(c)))
         return c.value
+
+    def set_profiling(self, on):
+        self._ck(self.lib.hmj_set_profiling(self.h, 1 if on else 0))
 
     def timings(self):
         t = Timings()

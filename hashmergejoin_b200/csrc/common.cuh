@@ -57,6 +57,10 @@ struct hmj_ctx {
   uint32_t lb_epoch = 0;
   void* lb_seen_ptr = nullptr;
   size_t lb_seen_bytes = 0;
+  // optional per-launch timing of the dominant kernel (onesweep pass), see hmj_set_profiling
+  bool prof_on = false;
+  std::vector<cudaEvent_t> prof_events;  // pairs: [2i] before, [2i+1] after launch i
+  size_t prof_used = 0;
   // last whole-operator result
   uint64_t last_pairs = 0;
   hmj_timings tm;

@@ -71,6 +71,7 @@ extern "C" int hmj_destroy(hmj_ctx* ctx) {
   hmj_release_workspace(ctx);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
+  for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

@@ -113,7 +113,23 @@ extern "C" int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out) {
   if (cudaEventElapsedTime(&ms, ctx->ev[EV_HASHED], ctx->ev[EV_SORTED]) == cudaSuccess) t.sort_ms = ms;
   if (cudaEventElapsedTime(&ms, ctx->ev[EV_SORTED], ctx->ev[EV_JOINED]) == cudaSuccess) t.join_ms = ms;
   if (cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_JOINED]) == cudaSuccess) t.total_ms = ms;
+  t.pass_ms_sum = 0;
+  t.pass_launches = 0;
+  for (size_t i = 0; i + 1 < ctx->prof_used; i += 2) {
+    if (cudaEventElapsedTime(&ms, ctx->prof_events[i], ctx->prof_events[i + 1]) == cudaSuccess) {
+      t.pass_ms_sum += ms;
+      t.pass_launches++;
+    }
+  }
   cudaGetLastError();  // events never recorded yet: not an error for the caller
   *out = t;
+  return HMJ_OK;
+}
+
+extern "C" int hmj_set_profiling(hmj_ctx* ctx, int on) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->prof_on = on != 0;
+  ctx->prof_used = 0;
   return HMJ_OK;
 }

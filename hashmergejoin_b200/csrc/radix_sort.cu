@@ -116,7 +116,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
                      uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                      uint32_t n, int shift, const uint32_t* __restrict__ bin_offsets,
                      uint64_t* __restrict__ lookback, uint32_t* __restrict__ tile_counter,
-                     uint32_t epoch) {
+                     uint32_t epoch, uint32_t iota_base) {
   using Cfg = OnesweepCfg<THREADS, ITEMS>;
   constexpr int WARPS = Cfg::WARPS;
   constexpr int TILE = Cfg::TILE;
@@ -230,7 +230,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     const uint32_t idx = warp_base + k * 32 + lane;
-    uint32_t v = idx;
+    uint32_t v = idx + iota_base;
     if (vals_in != nullptr && idx < n) v = __ldcs(vals_in + idx);
     s_vals[pos[k]] = v;
   }
@@ -260,16 +260,30 @@ __global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n) {
 template <int THREADS, int ITEMS, int MIN_BLOCKS>
 int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
                 uint32_t* vout, uint32_t n, int shift, const uint32_t* bins, uint64_t* lookback,
-                uint32_t* counter, uint32_t epoch) {
+                uint32_t* counter, uint32_t epoch, uint32_t iota_base = 0) {
   using Cfg = OnesweepCfg<THREADS, ITEMS>;
   // per-device attribute; cheap enough to set on every launch
   HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)Cfg::SMEM_BYTES));
   const uint32_t tiles = (uint32_t)hmj_div_up(n, Cfg::TILE);
+  cudaEvent_t ev_after = nullptr;
+  if (ctx->prof_on) {
+    if (ctx->prof_used + 2 > ctx->prof_events.size()) {
+      cudaEvent_t a, b;
+      HMJ_CUDA(ctx, cudaEventCreate(&a));
+      HMJ_CUDA(ctx, cudaEventCreate(&b));
+      ctx->prof_events.push_back(a);
+      ctx->prof_events.push_back(b);
+    }
+    HMJ_CUDA(ctx, cudaEventRecord(ctx->prof_events[ctx->prof_used], ctx->stream));
+    ev_after = ctx->prof_events[ctx->prof_used + 1];
+    ctx->prof_used += 2;
+  }
   onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
-      kin, vin, kout, vout, n, shift, bins, lookback, counter, epoch);
+      kin, vin, kout, vout, n, shift, bins, lookback, counter, epoch, iota_base);
   HMJ_LAUNCHED(ctx);
+  if (ev_after) HMJ_CUDA(ctx, cudaEventRecord(ev_after, ctx->stream));
   return HMJ_OK;
 }
 
@@ -488,6 +502,14 @@ extern "C" int hmj_partition_counts(hmj_ctx* ctx, const uint64_t* d_hash, size_t
 extern "C" int hmj_partition_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid,
                                    size_t n, int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
                                    uint64_t* d_part_offsets) {
+  return hmj_partition_pairs_base(ctx, d_hash, d_rowid, 0, n, bits, d_hash_out, d_rowid_out,
+                                  d_part_offsets);
+}
+
+extern "C" int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash,
+                                        const uint32_t* d_rowid, uint32_t rowid_base, size_t n,
+                                        int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
+                                        uint64_t* d_part_offsets) {
   if (!ctx) return HMJ_EARG;
   HMJ_ARG(ctx, bits >= 1 && bits <= 8 && d_part_offsets);
   HMJ_ARG(ctx, n < (size_t(1) << 32) - (size_t(1) << 16));
@@ -526,5 +548,5 @@ extern "C" int hmj_partition_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const u
   }
   const uint32_t epoch = ++ctx->lb_epoch;
   return launch_pass<256, 16, 3>(ctx, d_hash, d_rowid, d_hash_out, d_rowid_out, n32, 64 - bits,
-                                 d_hist, d_lb, d_counters, epoch);
+                                 d_hist, d_lb, d_counters, epoch, rowid_base);
 }

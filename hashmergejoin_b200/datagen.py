@@ -134,3 +134,39 @@ def zipf_indices(n_draws, n_keys, s=1.0, seed=7):
     cdf /= cdf[-1]
     u = rng.random(n_draws)
     return np.minimum(np.searchsorted(cdf, u), n_keys - 1).astype(np.int64)
+
+
+# ---- device-side generators (torch; harness only) for the full-size configurations -------
+def _lsr(x, s):
+    """logical shift right on int64 tensors (torch's >> is arithmetic)"""
+    return (x >> s) & ((1 << (64 - s)) - 1)
+
+
+def splitmix64_torch(x):
+    """Same bijection as splitmix64() on int64 tensors holding u64 bit patterns."""
+    import torch
+    c1 = torch.tensor(-7046029254386353131, dtype=torch.int64, device=x.device)   # 0x9E3779B97F4A7C15
+    c2 = torch.tensor(-4658895280553007687, dtype=torch.int64, device=x.device)   # 0xBF58476D1CE4E5B9
+    c3 = torch.tensor(-7723592293110705685, dtype=torch.int64, device=x.device)   # 0x94D049BB133111EB
+    x = x + c1
+    x = (x ^ _lsr(x, 30)) * c2
+    x = (x ^ _lsr(x, 27)) * c3
+    return x ^ _lsr(x, 31)
+
+
+def unique_u64_torch(n, seed=0, device="cuda", perm_mult=None, chunk=1 << 26):
+    """Device version of unique_u64: key[i] = splitmix64(idx(i) + (seed<<40)) with
+    idx(i) = i, or a permutation of 0..n-1 when perm_mult is given: idx(i) = (i*perm_mult + 12345)
+    mod n for n a power of two and odd perm_mult (a bijection), so two calls with different
+    perm_mult give the same key set in different row orders."""
+    import torch
+    out = torch.empty(n, dtype=torch.int64, device=device)
+    if perm_mult is not None:
+        assert n & (n - 1) == 0 and perm_mult % 2 == 1, "permutation needs n = 2^k and an odd multiplier"
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        idx = torch.arange(lo, hi, dtype=torch.int64, device=device)
+        if perm_mult is not None:
+            idx = (idx * perm_mult + 12345) & (n - 1)
+        out[lo:hi] = splitmix64_torch(idx + (seed << 40))
+    return out

@@ -161,6 +161,11 @@ int hmj_partition_counts(hmj_ctx* ctx, const uint64_t* d_hash, size_t n, int bit
 int hmj_partition_pairs(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid, size_t n,
                         int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
                         uint64_t* d_part_offsets);
+/* same, with row ids generated as rowid_base + input index when d_rowid is NULL: the multi-GPU
+ * path gives every rank's rows globally unique ids this way. */
+int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid,
+                             uint32_t rowid_base, size_t n, int bits, uint64_t* d_hash_out,
+                             uint32_t* d_rowid_out, uint64_t* d_part_offsets);
 int hmj_partition_counts_host(hmj_ctx* ctx, const uint64_t* h_hash, size_t n, int bits,
                               uint64_t* h_counts);
 
@@ -181,8 +186,15 @@ typedef struct hmj_timings {
   float h2d_ms, d2h_ms;
   float total_ms;
   uint32_t sort_passes; /* scatter passes actually executed (both relations) */
+  /* dominant kernel (onesweep pass) timed per launch while profiling is on */
+  float pass_ms_sum;     /* sum of the per-launch durations since profiling was (re)enabled */
+  uint32_t pass_launches;
 } hmj_timings;
 int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
+/* on != 0: bracket every onesweep-pass launch with CUDA events on the context's stream and
+ * reset the accumulated figures; 0: stop.  Used by bench.py for the roofline of the dominant
+ * kernel. */
+int hmj_set_profiling(hmj_ctx* ctx, int on);
 
 #ifdef __cplusplus
 }

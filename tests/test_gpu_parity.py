@@ -1,0 +1,319 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same
+seeded inputs, against the committed golden fixtures, and -- at full benchmark sizes -- through
+size-independent properties.  Bit-exact everywhere (integer/byte/index work)."""
+import numpy as np
+import pytest
+
+import hashmergejoin_b200 as hmj
+from hashmergejoin_b200 import datagen
+from tests import golden_util as G
+from tests.oracle_binding import Keys
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+
+
+def dev(a):
+    """numpy u64/u32/u8 -> device tensor with the same bits"""
+    a = np.ascontiguousarray(a)
+    view = {np.dtype(np.uint64): np.int64, np.dtype(np.uint32): np.int32}.get(a.dtype, None)
+    t = torch.from_numpy(a.view(view) if view else a)
+    return t.cuda()
+
+
+def host(t, dt):
+    return t.cpu().numpy().view(dt)
+
+
+# ------------------------------------------------------------------ K1 hashing
+def test_hash_golden_vectors(ctx):
+    g = G.load("std_hash_strings.json")
+    off, chars = datagen.strings_from_list([bytes.fromhex(s) for s in g["strings_hex"]])
+    chars = np.concatenate([chars, np.zeros(8, np.uint8)])
+    out = host(ctx.hash_strings(dev(off), dev(chars)), np.uint64)
+    assert np.array_equal(out, G.u64(g["hashes"]))
+
+
+def test_hash_random_all_lengths_and_alignments(ctx, oracle):
+    rng = np.random.default_rng(1)
+    items = [bytes(rng.integers(0, 256, size=ln, dtype=np.uint8)) for ln in range(0, 100) for _ in range(40)]
+    rng.shuffle(items)
+    off, chars = datagen.strings_from_list(items)
+    out = host(ctx.hash_strings(dev(off), dev(chars)), np.uint64)
+    assert np.array_equal(out, oracle.hash_strings(off, chars))
+    # same rows behind a 3-byte prefix: every row starts at another alignment
+    off3 = off + np.uint64(3)
+    chars3 = np.concatenate([np.array([1, 2, 3], np.uint8), chars])
+    out3 = host(ctx.hash_strings(dev(off3), dev(chars3)), np.uint64)
+    assert np.array_equal(out3, out)
+
+
+def test_hash_strgen_and_long_rows(ctx, oracle):
+    off, chars, _, _ = datagen.strgen(200000, seed=3)
+    out = host(ctx.hash_strings(dev(off), dev(chars)), np.uint64)
+    assert np.array_equal(out, oracle.hash_strings(off, chars))
+    # rows long enough that a 1024-row tile cannot be staged in shared memory
+    rng = np.random.default_rng(2)
+    items = [bytes(rng.integers(0, 256, size=int(ln), dtype=np.uint8)) for ln in rng.integers(0, 400, size=3000)]
+    off, chars = datagen.strings_from_list(items)
+    out = host(ctx.hash_strings(dev(off), dev(chars)), np.uint64)
+    assert np.array_equal(out, oracle.hash_strings(off, chars))
+
+
+def test_hash_u64_identity(ctx):
+    k = np.random.default_rng(0).integers(0, 2 ** 64, size=100001, dtype=np.uint64)
+    assert np.array_equal(host(ctx.hash_u64(dev(k)), np.uint64), k)
+
+
+# ------------------------------------------------------------------ K2/K3 sort
+def check_sort(ctx, oracle, keys, rowid=None):
+    keys = np.ascontiguousarray(keys, np.uint64)
+    h, r = ctx.sort_pairs(dev(keys), None if rowid is None else dev(rowid))
+    h, r = host(h, np.uint64), host(r, np.uint32)
+    rid = np.arange(keys.size, dtype=np.uint32) if rowid is None else rowid
+    # (1) hash column == reference order (== std::sort of the hashes)
+    oh, orow = oracle.radix_sort(keys, Keys(u64=keys), rowid=rid)
+    assert np.array_equal(h, oh)
+    # (2) same (hash,row) multiset; our sort is stable so it IS the canonical order
+    ch, cr = oracle.canonical(oh, orow)
+    if rowid is None:
+        assert np.array_equal(r, cr)
+    else:
+        assert np.array_equal(keys[np.argsort(keys, kind="stable")], h)
+        assert np.array_equal(rid[np.argsort(keys, kind="stable")], r)
+
+
+@pytest.mark.parametrize("case", [np.arange(4, -1, -1), np.arange(5, 0, -1), np.arange(12345, 0, -1),
+                                  np.arange(1 << 18, 0, -1)])
+def test_sort_reference_ladder(ctx, oracle, case):
+    # radix_hash_test.cc:40-120 (+ in-place variants :122-193): reversed ranges
+    check_sort(ctx, oracle, case.astype(np.uint64))
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 4095, 4096, 4097, 1 << 16, 100003, (1 << 20) + 5])
+def test_sort_random_u64(ctx, oracle, n):
+    # radix_hash_test.cc:195-212,244-262 / radix_sort_test.cc:27-68: random u64 vs std::sort
+    check_sort(ctx, oracle, np.random.default_rng(n).integers(0, 2 ** 64, size=n, dtype=np.uint64))
+
+
+def test_sort_top_bit_and_duplicates(ctx, oracle):
+    top = np.empty(1024, np.uint64)  # radix_hash_test.cc:227-242
+    top[0::2] = (np.uint64(1) << np.uint64(63)) + np.arange(512, dtype=np.uint64)
+    top[1::2] = np.arange(512, dtype=np.uint64)
+    check_sort(ctx, oracle, top)
+    rng = np.random.default_rng(9)
+    check_sort(ctx, oracle, rng.integers(0, 7, size=50000, dtype=np.uint64))          # heavy duplicates
+    check_sort(ctx, oracle, np.full(9000, 0xFFFFFFFFFFFFFFFF, np.uint64))             # all max
+    check_sort(ctx, oracle, rng.integers(0, 2 ** 64, size=30000, dtype=np.uint64) | np.uint64(0xFF))
+    vals = rng.permutation(70000).astype(np.uint32)                                   # explicit payloads
+    check_sort(ctx, oracle, rng.integers(0, 1000, size=70000, dtype=np.uint64), rowid=vals)
+
+
+def test_sort_skips_trivial_passes_large(ctx, oracle):
+    n = (1 << 22) + 17  # above the skip threshold: keys < 2^20 -> only 3 passes run
+    keys = np.random.default_rng(5).integers(0, 1 << 20, size=n, dtype=np.uint64)
+    check_sort(ctx, oracle, keys)
+    # in place (input aliases output) with an odd number of executed passes
+    t = dev(keys)
+    r = torch.empty(n, dtype=torch.int32, device="cuda")
+    ctx.sort_pairs(t, None, out_hash=t, out_rowid=r)
+    assert np.array_equal(host(t, np.uint64), np.sort(keys))
+    assert np.array_equal(keys[host(r, np.uint32)], np.sort(keys))
+
+
+def test_sort_empty(ctx):
+    h, r = ctx.sort_pairs(torch.empty(0, dtype=torch.int64, device="cuda"))
+    assert h.numel() == 0 and r.numel() == 0
+
+
+def test_hash_sort_strings_golden_and_oracle(ctx, oracle):
+    g = G.load("strgen_join_600.json")
+    off, chars = np.array(g["r_offsets"], np.uint64), G.u8(g["r_chars_hex"])
+    h, r = ctx.hash_sort_strings(dev(off), dev(np.concatenate([chars, np.zeros(8, np.uint8)])))
+    assert np.array_equal(host(h, np.uint64), G.u64(g["r_sorted_hash"]))   # reference's sorted hashes
+    assert np.array_equal(host(r, np.uint32), np.array(g["r_sorted_rowid"], np.uint32))  # unique hashes
+    off, chars, _, _ = datagen.strgen(300000, seed=4)
+    h, r = ctx.hash_sort_strings(dev(off), dev(chars))
+    k = Keys(offsets=off, chars=chars)
+    oh, orow = oracle.canonical(*oracle.radix_sort(oracle.hashes(k), k))
+    assert np.array_equal(host(h, np.uint64), oh) and np.array_equal(host(r, np.uint32), orow)
+
+
+# ------------------------------------------------------------------ K4-K6 merge join
+def gpu_join_u64(ctx, rk, sk):
+    rh, rr = ctx.hash_sort_u64(dev(rk))
+    sh, sr = ctx.hash_sort_u64(dev(sk))
+    R, S = hmj.SortedRelation(rh, rr), hmj.SortedRelation(sh, sr)
+    out_r, out_s = ctx.merge_join(R, S)
+    m, sm = ctx.merge_join_aggregate(R, S)
+    return host(out_r, np.uint32), host(out_s, np.uint32), m, sm
+
+
+def check_join_u64(ctx, oracle, rk, sk):
+    rk, sk = np.ascontiguousarray(rk, np.uint64), np.ascontiguousarray(sk, np.uint64)
+    out_r, out_s, m, sm = gpu_join_u64(ctx, rk, sk)
+    t_r, t_s, t_sum = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+    assert m == t_r.size and sm == t_sum
+    return out_r, out_s
+
+
+def test_join_unique_u64(ctx, oracle):
+    keys = datagen.unique_u64(100000, seed=1)
+    out_r, _ = check_join_u64(ctx, oracle, datagen.permuted(keys, 1), datagen.permuted(keys, 2))
+    assert out_r.size == 100000
+
+
+def test_join_golden_duplicates(ctx, oracle):
+    g = G.load("dup_join_u64.json")
+    rk, sk = G.u64(g["r_keys"]), G.u64(g["s_keys"])
+    out_r, out_s = check_join_u64(ctx, oracle, rk, sk)
+    # every pair the reference emits is in our result (ours is the full cross product)
+    assert set(zip(g["join_r"], g["join_s"])) <= set(zip(out_r.tolist(), out_s.tolist()))
+
+
+@pytest.mark.parametrize("nr,ns,rng_hi", [(0, 10, 5), (10, 0, 5), (1, 1, 1), (1, 3, 1), (5000, 7000, 600),
+                                          (30000, 100, 50), (100, 30000, 50), (20000, 20000, 2 ** 63)])
+def test_join_shapes(ctx, oracle, nr, ns, rng_hi):
+    rng = np.random.default_rng(nr * 7 + ns)
+    check_join_u64(ctx, oracle, rng.integers(0, rng_hi, size=nr, dtype=np.uint64),
+                   rng.integers(0, rng_hi, size=ns, dtype=np.uint64))
+
+
+def test_join_runs_longer_than_a_tile(ctx, oracle):
+    # a 9000-row S run against 3 R rows and vice versa: runs cross many merge-path tiles
+    rk = np.concatenate([np.full(3, 42), np.arange(100, 6000), np.full(9000, 77)]).astype(np.uint64)
+    sk = np.concatenate([np.full(9000, 42), np.arange(3000, 9000), np.full(2, 77)]).astype(np.uint64)
+    check_join_u64(ctx, oracle, rk, sk)
+
+
+def test_join_where_reference_is_exact(ctx, oracle):
+    # unique keys + maximal non-matching sentinels: here oracle walk == reference == true join
+    keys = datagen.unique_u64(20000, seed=8) >> np.uint64(1)
+    rk = np.concatenate([datagen.permuted(keys, 3), [np.uint64(2 ** 64 - 1)]]).astype(np.uint64)
+    sk = np.concatenate([datagen.permuted(keys, 4), [np.uint64(2 ** 64 - 2)]]).astype(np.uint64)
+    out_r, out_s = check_join_u64(ctx, oracle, rk, sk)
+    r, s = Keys(u64=rk), Keys(u64=sk)
+    rh, rr = oracle.radix_sort(rk, r)
+    sh, sr = oracle.radix_sort(sk, s)
+    w_r, w_s = oracle.merge_walk_reference(rh, rr, sh, sr, r, s)
+    assert all(np.array_equal(a, b) for a, b in zip(oracle.sort_pairs(w_r, w_s), oracle.sort_pairs(out_r, out_s)))
+
+
+def gpu_join_strings(ctx, off, chars, off2, chars2):
+    d_off, d_chars, d_off2, d_chars2 = dev(off), dev(chars), dev(off2), dev(chars2)
+    m = ctx.join_strings(d_off, d_chars, d_off2, d_chars2)
+    return ctx.join_result_to_host(m)
+
+
+def test_join_strings_golden(ctx, oracle):
+    g = G.load("strgen_join_600.json")
+    off, chars = np.array(g["r_offsets"], np.uint64), G.u8(g["r_chars_hex"])
+    off2, chars2 = np.array(g["s_offsets"], np.uint64), G.u8(g["s_chars_hex"])
+    out_r, out_s = gpu_join_strings(ctx, off, chars, off2, chars2)
+    ours = set(zip(out_r.tolist(), out_s.tolist()))
+    assert set(zip(g["join_r"], g["join_s"])) <= ours and len(ours) == 600
+
+
+def test_join_strings_vs_oracle_with_duplicates_and_hash_collisions(ctx, oracle):
+    off, chars, _, _ = datagen.strgen(50000, seed=6, shuffle_seed=1)
+    rng = np.random.default_rng(3)
+    pick_r = rng.integers(0, 50000, size=60000)   # duplicates on both sides (N:M)
+    pick_s = rng.integers(0, 50000, size=40000)
+    roff, rchars = datagen.take_rows(off, chars, pick_r)
+    soff, schars = datagen.take_rows(off, chars, pick_s)
+    out_r, out_s = gpu_join_strings(ctx, roff, rchars, soff, schars)
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars))
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+
+
+def test_join_verifies_keys_on_forced_hash_collisions(ctx, oracle):
+    # same hash column, different keys: feed the merge join pre-"hashed" columns that collide
+    items_r = [b"alpha", b"beta", b"gamma", b"delta"]
+    items_s = [b"alpha", b"BETA", b"gamma", b"delta", b"alpha"]
+    roff, rchars = datagen.strings_from_list(items_r)
+    soff, schars = datagen.strings_from_list(items_s)
+    rh = np.array([5, 5, 5, 9], np.uint64)       # all of alpha/beta/gamma "collide"
+    sh = np.array([5, 5, 5, 9, 5], np.uint64)
+    d = lambda a: dev(np.concatenate([a, np.zeros(8, a.dtype)])) if a.dtype == np.uint8 else dev(a)
+    rhs, rrs = ctx.sort_pairs(dev(rh))
+    shs, srs = ctx.sort_pairs(dev(sh))
+    R = hmj.SortedRelation(rhs, rrs, hmj.KEY_STRING, d(roff), d(rchars))
+    S = hmj.SortedRelation(shs, srs, hmj.KEY_STRING, d(soff), d(schars))
+    out_r, out_s = ctx.merge_join(R, S)
+    got = sorted(zip(host(out_r, np.uint32).tolist(), host(out_s, np.uint32).tolist()))
+    assert got == [(0, 0), (0, 4), (2, 2), (3, 3)]
+    assert ctx.merge_join_count(R, S) == 4
+
+
+# ------------------------------------------------------------------ whole operator, host buffers
+def test_join_host_api(ctx, oracle):
+    keys = datagen.unique_u64(50000, seed=2)
+    rk, sk = datagen.permuted(keys, 5), datagen.permuted(keys, 6)[:40000]
+    out_r, out_s = np.empty(50000, np.uint32), np.empty(50000, np.uint32)
+    m = ctx.join_u64_host(rk, sk, out_r, out_s)
+    assert m == 40000
+    assert np.array_equal(rk[out_r[:m]], sk[out_s[:m]])
+    t_r, t_s, _ = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+    c_r, c_s = oracle.sort_pairs(out_r[:m], out_s[:m])
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+    with pytest.raises(hmj.HmjError):
+        ctx.join_u64_host(rk, sk, np.empty(10, np.uint32), np.empty(10, np.uint32))  # HMJ_ECAPACITY
+    off, chars, _, _ = datagen.strgen(30000, seed=7, shuffle_seed=1)
+    off2, chars2, _, _ = datagen.strgen(30000, seed=7, shuffle_seed=2)
+    out_r, out_s = np.empty(30000, np.uint32), np.empty(30000, np.uint32)
+    assert ctx.join_strings_host(off, chars, off2, chars2, out_r, out_s) == 30000
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=off, chars=chars), Keys(offsets=off2, chars=chars2))
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+
+
+def test_sort_host_api(ctx, oracle):
+    keys = np.random.default_rng(8).integers(0, 2 ** 64, size=77777, dtype=np.uint64)
+    h, r = ctx.hash_sort_u64_host(keys)
+    assert np.array_equal(h, np.sort(keys)) and np.array_equal(keys[r], h)
+    h2, r2 = ctx.sort_pairs_host(keys, np.arange(keys.size, dtype=np.uint32)[::-1].copy())
+    assert np.array_equal(h2, h)
+
+
+# ------------------------------------------------------------------ A6 partitioning
+def test_partition_reference_case_and_oracle(ctx, oracle):
+    top = np.uint64(1) << np.uint64(63)   # partitioned_hash_test.cc:14-46
+    i = np.arange(5, dtype=np.uint64)
+    keys = np.stack([i, i | top, i | top | np.uint64(1024)], axis=1).reshape(-1)
+    assert ctx.partition_counts_host(keys, 1).tolist() == [5, 10]
+    g = G.load("partition_u64.json")
+    keys = G.u64(g["keys"])
+    for bits, counts in g["counts"].items():
+        assert ctx.partition_counts_host(keys, int(bits)).tolist() == counts
+    big = np.random.default_rng(1).integers(0, 2 ** 64, size=300000, dtype=np.uint64)
+    for bits in (1, 3, 8, 12, 14, 16):
+        assert np.array_equal(ctx.partition_counts_host(big, bits), oracle.partition_counts(big, bits))
+    for bits in (1, 3, 8):
+        oh, orow, offs = ctx.partition_pairs(dev(big), None, bits)
+        oh, orow, offs = host(oh, np.uint64), host(orow, np.uint32), host(offs, np.uint64)
+        part = (big >> np.uint64(64 - bits)).astype(np.int64)
+        order = np.argsort(part, kind="stable")
+        assert np.array_equal(orow, order.astype(np.uint32)) and np.array_equal(oh, big[order])
+        assert np.array_equal(np.diff(offs), oracle.partition_counts(big, bits))
+
+
+# ------------------------------------------------------------------ A7 hash-join baseline
+def test_hashjoin_baseline_vs_oracle(ctx, oracle):
+    rng = np.random.default_rng(12)
+    rk = rng.integers(0, 30000, size=50000, dtype=np.uint64)
+    sk = rng.integers(0, 30000, size=20000, dtype=np.uint64)
+    sk[5] = np.uint64(2 ** 64 - 1)
+    rk[7] = np.uint64(2 ** 64 - 1)
+    R = hmj.SortedRelation(dev(rk), None)
+    S = hmj.SortedRelation(dev(sk), None)
+    assert ctx.hashjoin_build_probe(R, S) == oracle.hash_join_raw(Keys(u64=rk), Keys(u64=sk))
+    off, chars, _, _ = datagen.strgen(20000, seed=6)
+    roff, rchars = datagen.take_rows(off, chars, rng.integers(0, 20000, size=30000))
+    soff, schars = datagen.take_rows(off, chars, rng.integers(0, 20000, size=15000))
+    rkeys, skeys = Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars)
+    R = hmj.SortedRelation(dev(oracle.hashes(rkeys)), None, hmj.KEY_STRING, dev(roff), dev(rchars))
+    S = hmj.SortedRelation(dev(oracle.hashes(skeys)), None, hmj.KEY_STRING, dev(soff), dev(schars))
+    assert ctx.hashjoin_build_probe(R, S) == oracle.hash_join_raw(rkeys, skeys)
