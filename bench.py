@@ -34,6 +34,7 @@ WORKLOADS = {
     "c3": (256 * 2 ** 20, "hash-merge join 256M x 256M 64-bit int keys, 1:1 match rate, 1 B200"),
     "c4": (2 ** 30, "hash-merge join 1B x 1B int keys radix-partitioned across N B200 with NCCL all-to-all"),
     "small": (2 ** 22, "hash-merge join 4M x 4M 64-bit int keys (smoke-sized)"),
+    "mid": (2 ** 26, "hash-merge join 64M x 64M 64-bit int keys (profiling-sized)"),
 }
 CPU_SAMPLE_ROWS = 16 * 2 ** 20  # rows per side of the bounded CPU sample
 
