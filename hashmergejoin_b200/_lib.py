@@ -41,6 +41,7 @@ class Timings(C.Structure):
         ("join_ms", C.c_float), ("h2d_ms", C.c_float), ("d2h_ms", C.c_float),
         ("total_ms", C.c_float), ("sort_passes", C.c_uint32),
         ("pass_ms_sum", C.c_float), ("pass_launches", C.c_uint32),
+        ("sort_finishes", C.c_uint32), ("sort_fallbacks", C.c_uint32),
     ]
 
 

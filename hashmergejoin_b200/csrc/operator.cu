@@ -39,6 +39,8 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   HMJ_ARG(ctx, (nr == 0 || d_rkeys) && (ns == 0 || d_skeys));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->tm.sort_passes = 0;
+  ctx->tm.sort_finishes = 0;
+  ctx->tm.sort_fallbacks = 0;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));  // identity hash: no kernel
   hmj_relation R = {}, S = {};
@@ -62,6 +64,8 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   HMJ_ARG(ctx, (nr == 0 || d_roffsets) && (ns == 0 || d_soffsets));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->tm.sort_passes = 0;
+  ctx->tm.sort_finishes = 0;
+  ctx->tm.sort_fallbacks = 0;
   uint64_t *rh = nullptr, *sh = nullptr;
   uint32_t *rr = nullptr, *sr = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_R_HASH, nr, &rh));

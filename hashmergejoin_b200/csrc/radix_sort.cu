@@ -60,25 +60,34 @@ radix_histogram_kernel(const uint64_t* __restrict__ keys, size_t n, uint32_t* __
   }
 }
 
-// One block per digit position: exclusive scan of its 256 bins (in place) and a flag telling
-// whether the pass is trivial (one bin holds every key).
+// One block per digit position: exclusive scan of its 256 bins (in place) plus the statistics
+// the host planner reads back: g_stats[2p] = number of non-empty bins, g_stats[2p+1] = largest
+// bin (== n means the digit is trivial: every key shares it and the pass can be skipped).
 __global__ void __launch_bounds__(RADIX)
-radix_scan_kernel(uint32_t* __restrict__ g_hist, uint32_t n32, uint32_t* __restrict__ g_skip) {
+radix_scan_kernel(uint32_t* __restrict__ g_hist, uint32_t n32, uint32_t* __restrict__ g_stats) {
   __shared__ uint32_t s_warp[RADIX / 32];
+  __shared__ uint32_t s_max[RADIX / 32];
   const int p = blockIdx.x, d = threadIdx.x, lane = d & 31, w = d >> 5;
   const uint32_t c = g_hist[p * RADIX + d];
-  uint32_t x = c;
+  uint32_t x = c, mx = c;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
     const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
     if (lane >= o) x += y;
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   }
   if (lane == 31) s_warp[w] = x;
-  const int trivial = __syncthreads_or(c == n32);
+  if (lane == 0) s_max[w] = mx;
+  const int nz = __syncthreads_count(c != 0);
   uint32_t pre = 0;
   for (int i = 0; i < w; ++i) pre += s_warp[i];
   g_hist[p * RADIX + d] = pre + x - c;
-  if (d == 0) g_skip[p] = trivial ? 1u : 0u;
+  if (d == 0) {
+    uint32_t m = 0;
+    for (int i = 0; i < RADIX / 32; ++i) m = max(m, s_max[i]);
+    g_stats[2 * p] = (uint32_t)nz;
+    g_stats[2 * p + 1] = m;
+  }
 }
 
 // ---------------------------------------------------------------- K3: onesweep pass
@@ -110,7 +119,7 @@ struct OnesweepCfg {
 
 // keys_in/vals_in -> keys_out/vals_out, stable on digit (key >> shift) & 255.
 // vals_in == nullptr means the payload is the element's global index (row id iota).
-template <int THREADS, int ITEMS, int MIN_BLOCKS>
+template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -156,7 +165,21 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
 #pragma unroll
   for (int k = 0; k < ITEMS; ++k) {
     const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
-    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    uint32_t peers;
+    if (RANK_MODE == 0) {
+      // MATCH.ANY runs on the ADU pipe (about 65 cycles per warp instruction per SM measured,
+      // profiles/r1a_*): kept only for comparison
+      peers = __match_any_sync(0xffffffffu, d);
+    } else {
+      // one ballot per digit bit: lanes whose digit agrees with mine on every bit
+      peers = 0xffffffffu;
+#pragma unroll
+      for (int b = 0; b < RADIX_BITS; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const uint32_t m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+      }
+    }
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
     if (lane == leader) {
@@ -257,13 +280,13 @@ __global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = i;
 }
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS>
+template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE = 1>
 int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
                 uint32_t* vout, uint32_t n, int shift, const uint32_t* bins, uint64_t* lookback,
                 uint32_t* counter, uint32_t epoch, uint32_t iota_base = 0) {
   using Cfg = OnesweepCfg<THREADS, ITEMS>;
   // per-device attribute; cheap enough to set on every launch
-  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS>,
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)Cfg::SMEM_BYTES));
   const uint32_t tiles = (uint32_t)hmj_div_up(n, Cfg::TILE);
@@ -280,7 +303,7 @@ int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t
     ev_after = ctx->prof_events[ctx->prof_used + 1];
     ctx->prof_used += 2;
   }
-  onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
+  onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
       kin, vin, kout, vout, n, shift, bins, lookback, counter, epoch, iota_base);
   HMJ_LAUNCHED(ctx);
   if (ev_after) HMJ_CUDA(ctx, cudaEventRecord(ev_after, ctx->stream));
@@ -288,12 +311,9 @@ int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t
 }
 
 int sort_cfg_from_env() {
-  static int cfg = -1;
-  if (cfg < 0) {
-    const char* e = getenv("HMJ_SORT_CFG");
-    cfg = e ? atoi(e) : 0;
-  }
-  return cfg;
+  // tuning knob for scripts/sort_sweep.py; read per call so one process can sweep
+  const char* e = getenv("HMJ_SORT_CFG");
+  return e ? atoi(e) : 0;
 }
 
 int tile_items_for_cfg(int cfg) {
@@ -302,12 +322,169 @@ int tile_items_for_cfg(int cfg) {
     case 2: return OnesweepCfg<256, 24>::TILE;
     case 3: return OnesweepCfg<384, 16>::TILE;
     case 4: return OnesweepCfg<512, 16>::TILE;
+    case 5: return OnesweepCfg<256, 16>::TILE;  // MATCH.ANY ranking (round-1a kernel)
+    case 6: return OnesweepCfg<512, 12>::TILE;
+    case 7: return OnesweepCfg<384, 20>::TILE;
     default: return OnesweepCfg<256, 16>::TILE;
   }
 }
 
 }  // namespace
 
+// ---------------------------------------------------------------- bucket finish (hybrid sort)
+// After the scatter passes over the top digits the array is ordered on the prefix
+// key >> shift, stable inside a bucket.  This kernel finishes every bucket by rank-by-counting
+// on the full key (ties keep their order, so the whole sort stays stable): it stands in for the
+// reference's small-bucket insertion sort (radix_hash.h:86-120,147-150).  A CTA owns the
+// buckets that START in its tile and sees FIN_HALO elements past the tile end; a bucket that
+// does not fit in that window or exceeds FIN_MAX_BUCKET raises *flag and the host re-sorts
+// with scatter passes over every digit.  One read + one write of the pairs.
+namespace {
+constexpr int FIN_THREADS = 256;
+constexpr int FIN_TILE = 2048;
+constexpr int FIN_HALO = 512;
+constexpr int FIN_MAX_BUCKET = 512;
+constexpr int FIN_SPAN = FIN_TILE + FIN_HALO;
+
+// fast path data: one 32-bit word per element = (31 key bits just below the prefix) << 1 | head
+// flag (first element of its bucket).  Ranking walks compare these words; two bucket-mates that
+// agree on all 31 bits but differ in the full key (possible only when shift > 31) send the
+// tile to the slow path, which repeats the walks on the full 64-bit keys.
+__global__ void __launch_bounds__(FIN_THREADS)
+bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
+                     int shift, uint32_t* __restrict__ flag) {
+  __shared__ uint64_t s_k[FIN_SPAN + 1];   // [0] = element before the tile
+  __shared__ uint32_t s_sub[FIN_SPAN + 1]; // [avail] = sentinel head
+  __shared__ uint16_t s_src[FIN_SPAN + 1]; // source index of the element ranked at a position
+  __shared__ uint32_t s_tie;
+  const uint32_t tile_start = blockIdx.x * (uint32_t)FIN_TILE;
+  const uint32_t avail = min((uint32_t)FIN_SPAN, n - tile_start);
+  const int tid = threadIdx.x;
+  const bool has_pred = tile_start != 0;
+  if (tid == 0) {
+    s_k[0] = has_pred ? keys_in[tile_start - 1] : 0;
+    s_tie = 0;
+  }
+  for (uint32_t i = tid; i < avail; i += FIN_THREADS) s_k[1 + i] = keys_in[tile_start + i];
+  __syncthreads();
+  const int sub_shift = shift > 31 ? shift - 31 : 0;
+  const uint64_t sub_mask = shift >= 31 ? 0x7fffffffull : ((1ull << shift) - 1);
+  for (uint32_t i = tid; i <= avail; i += FIN_THREADS) {
+    uint32_t w = 1u;  // sentinel
+    if (i < avail) {
+      const uint64_t key = s_k[1 + i], prev = s_k[i];
+      const bool head = (i == 0) || (shift < 64 && ((key ^ prev) >> shift) != 0);
+      w = ((uint32_t)((key >> sub_shift) & sub_mask) << 1) | (head ? 1u : 0u);
+    }
+    s_sub[i] = w;
+    s_src[i] = 0xffff;
+  }
+  __syncthreads();
+  // the bucket at the tile start belongs to the previous tile when it began there
+  const bool straddle = has_pred && (shift >= 64 || ((s_k[1] ^ s_k[0]) >> shift) == 0);
+  const bool more_after = tile_start + avail < n;
+
+  uint32_t my_pos[(FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS];
+#pragma unroll
+  for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
+    const uint32_t i = it * FIN_THREADS + tid;
+    my_pos[it] = 0xffffffffu;
+    if (i >= avail) continue;
+    const uint32_t me = s_sub[i];
+    const uint32_t me_le = me | 1u, me_lt = me & ~1u;
+    uint32_t rank = 0, o = me, j = i;
+    while (!(o & 1u)) {
+      --j;
+      o = s_sub[j];
+      rank += (o <= me_le) ? 1u : 0u;
+    }
+    const uint32_t start = j;
+    if (start >= (uint32_t)FIN_TILE || (start == 0 && straddle)) continue;  // not owned here
+    uint32_t e = i + 1;
+    o = s_sub[e];
+    while (!(o & 1u)) {
+      rank += (o < me_lt) ? 1u : 0u;
+      ++e;
+      o = s_sub[e];
+    }
+    if ((e == avail && more_after) || e - start > (uint32_t)FIN_MAX_BUCKET) {
+      if (i == start) atomicOr(flag, 1u);
+      continue;
+    }
+    my_pos[it] = start + rank;
+    s_src[start + rank] = (uint16_t)i;
+  }
+  __syncthreads();
+  // tie check: my successor in ranked order, if a bucket-mate with the same 31 bits, must
+  // also have the same full key
+  if (shift > 31) {
+#pragma unroll
+    for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
+      const uint32_t i = it * FIN_THREADS + tid;
+      const uint32_t p = my_pos[it];
+      if (p == 0xffffffffu) continue;
+      const uint32_t nxt = s_src[p + 1];
+      if (nxt == 0xffff) continue;
+      if (((s_sub[nxt] ^ s_sub[i]) >> 1) == 0 &&
+          (shift >= 64 || ((s_k[1 + nxt] ^ s_k[1 + i]) >> shift) == 0) &&
+          s_k[1 + nxt] != s_k[1 + i])
+        s_tie = 1;
+    }
+    __syncthreads();
+  }
+  if (s_tie == 0) {
+#pragma unroll
+    for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
+      const uint32_t i = it * FIN_THREADS + tid;
+      const uint32_t p = my_pos[it];
+      if (p == 0xffffffffu) continue;
+      keys_out[tile_start + p] = s_k[1 + i];
+      vals_out[tile_start + p] = vals_in ? vals_in[tile_start + i] : tile_start + i;
+    }
+    return;
+  }
+  // slow path: same ranking on the full keys
+  const uint64_t low_mask = shift >= 64 ? ~0ull : ((1ull << shift) - 1);
+  for (uint32_t i = tid; i < avail; i += FIN_THREADS) {
+    const uint64_t key = s_k[1 + i];
+    const uint64_t lo = key & ~low_mask, hi = key | low_mask;  // key range of my bucket
+    uint32_t rank = 0;
+    int j = (int)i - 1;
+    while (j >= 0) {
+      const uint64_t o = s_k[1 + j];
+      if (o < lo) break;
+      rank += (o <= key) ? 1u : 0u;
+      --j;
+    }
+    const uint32_t start = (uint32_t)(j + 1);
+    if (start >= (uint32_t)FIN_TILE) continue;
+    if (j < 0 && has_pred && s_k[0] >= lo) continue;
+    uint32_t e = i + 1;
+    while (e < avail) {
+      const uint64_t o = s_k[1 + e];
+      if (o > hi) break;
+      rank += (o < key) ? 1u : 0u;
+      ++e;
+    }
+    if ((e == avail && more_after) || e - start > (uint32_t)FIN_MAX_BUCKET) continue;  // flagged above
+    const uint32_t dst = tile_start + start + rank;
+    keys_out[dst] = key;
+    vals_out[dst] = vals_in ? vals_in[tile_start + i] : tile_start + i;
+  }
+}
+
+struct DigitStats { uint32_t nz, maxbin; };
+
+int hybrid_from_env() {
+  const char* e = getenv("HMJ_SORT_HYBRID");
+  return e ? atoi(e) : 1;
+}
+
+}  // namespace
+
+// Plans and runs one sort.  Steps alternate between (keys_out,vals_out) and the workspace
+// ping-pong pair; the last step always lands in the output pair.
 int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in, size_t n,
                   uint64_t* keys_out, uint32_t* vals_out) {
   HMJ_ARG(ctx, n < (size_t(1) << 32) - (size_t(1) << 16));
@@ -320,37 +497,77 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   const int tile_items = tile_items_for_cfg(cfg);
   const size_t tiles = hmj_div_up(n, tile_items);
 
-  // scratch: [8*256 bins][8 skip flags][8 tile counters]
+  // scratch: [8*256 bins][16 stats][24 tile counters][8 flags]
+  constexpr int MAX_LAUNCHED_PASSES = 24;
   uint32_t* d_hist = nullptr;
-  const size_t hist_words = NUM_PASSES * RADIX + 2 * NUM_PASSES;
+  const size_t hist_words = NUM_PASSES * RADIX + 2 * NUM_PASSES + MAX_LAUNCHED_PASSES + 8;
   HMJ_TRY(hmj_ws(ctx, WS_HIST, hist_words, &d_hist));
-  uint32_t* d_skip = d_hist + NUM_PASSES * RADIX;
-  uint32_t* d_counters = d_skip + NUM_PASSES;
+  uint32_t* d_stats = d_hist + NUM_PASSES * RADIX;
+  uint32_t* d_counters = d_stats + 2 * NUM_PASSES;
+  uint32_t* d_flag = d_counters + MAX_LAUNCHED_PASSES;
   HMJ_CUDA(ctx, cudaMemsetAsync(d_hist, 0, hist_words * sizeof(uint32_t), st));
 
   const size_t chunk = (size_t)HIST_THREADS * HIST_ITEMS;
   const int hgrid = (int)min(hmj_div_up(n, chunk), (size_t)ctx->num_sms * 4);
   radix_histogram_kernel<<<hgrid, HIST_THREADS, 0, st>>>(keys_in, n, d_hist);
   HMJ_LAUNCHED(ctx);
-  radix_scan_kernel<<<NUM_PASSES, RADIX, 0, st>>>(d_hist, n32, d_skip);
+  radix_scan_kernel<<<NUM_PASSES, RADIX, 0, st>>>(d_hist, n32, d_stats);
   HMJ_LAUNCHED(ctx);
 
-  // Trivial passes (all keys share the digit) are skipped when the relation is large enough
-  // for a pass to cost more than the read-back of 8 flags.
-  bool skip[NUM_PASSES] = {};
-  if (n >= (size_t(1) << 21)) {
-    uint32_t* h_skip = reinterpret_cast<uint32_t*>(ctx->pinned);
-    HMJ_CUDA(ctx, cudaMemcpyAsync(h_skip, d_skip, NUM_PASSES * sizeof(uint32_t),
+  // ---- plan (host): which digits need a scatter pass, and whether a prefix sort + bucket
+  // finish is enough.  Small sorts skip the read-back and run every pass.
+  DigitStats stats[NUM_PASSES];
+  for (int p = 0; p < NUM_PASSES; ++p) stats[p] = {RADIX, 0};
+  const bool planned = n >= (size_t(1) << 15);
+  if (planned) {
+    uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_stats, 2 * NUM_PASSES * sizeof(uint32_t),
                                   cudaMemcpyDeviceToHost, st));
     HMJ_CUDA(ctx, cudaStreamSynchronize(st));
-    for (int p = 0; p < NUM_PASSES; ++p) skip[p] = h_skip[p] != 0;
+    for (int p = 0; p < NUM_PASSES; ++p) stats[p] = {h[2 * p], h[2 * p + 1]};
   }
-  int P = 0;
-  for (int p = 0; p < NUM_PASSES; ++p) P += skip[p] ? 0 : 1;
-  ctx->tm.sort_passes += (uint32_t)P;
+  bool trivial[NUM_PASSES];
+  for (int p = 0; p < NUM_PASSES; ++p) trivial[p] = planned && stats[p].maxbin == n32;
 
+  int digits[NUM_PASSES], nd = 0;  // scatter passes of the first attempt, ascending
+  int finish_shift = -1;           // >= 0: bucket finish on key >> finish_shift
+  bool hybrid = hybrid_from_env() != 0 && (planned || n <= (size_t)FIN_MAX_BUCKET);
+  if (hybrid) {
+    // include top digits until the prefix separates the keys into buckets of <= ~16..32
+    const double need = n <= (size_t)FIN_MAX_BUCKET / 2 ? 0.0 : floor(log2((double)n)) - 4.0;
+    double eff = 0;
+    int q = 0, nontrivial = 0;
+    bool skewed = false;
+    while (q < NUM_PASSES && eff < need) {
+      const int d = NUM_PASSES - 1 - q;
+      if (!trivial[d]) {
+        const double mean = (double)n / stats[d].nz;
+        if ((double)stats[d].maxbin > mean + 8.0 * sqrt(mean) + 64.0) skewed = true;
+        eff += log2((double)stats[d].nz);
+        ++nontrivial;
+      }
+      ++q;
+    }
+    if (skewed || eff < need || nontrivial >= NUM_PASSES - 1) {
+      hybrid = false;
+    } else {
+      finish_shift = RADIX_BITS * (NUM_PASSES - q);
+      if (finish_shift == 0) finish_shift = -1;  // the prefix is the whole key: plain LSD sort
+      for (int d = NUM_PASSES - q; d < NUM_PASSES; ++d)
+        if (!trivial[d]) digits[nd++] = d;
+    }
+  }
+  if (!hybrid) {
+    nd = 0;
+    for (int d = 0; d < NUM_PASSES; ++d)
+      if (!trivial[d]) digits[nd++] = d;
+  }
+
+  struct Buf { uint64_t* k; uint32_t* v; };
+  Buf bufs[2] = {{keys_out, vals_out}, {nullptr, nullptr}};
   const bool aliased = (keys_in == keys_out) || (vals_in != nullptr && vals_in == vals_out);
-  if (P == 0) {
+  int steps = nd + (finish_shift >= 0 ? 1 : 0);
+  if (steps == 0) {  // nothing to do: copy through
     if (keys_in != keys_out)
       HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
     if (vals_in == nullptr) {
@@ -361,51 +578,116 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
     }
     return HMJ_OK;
   }
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, n, &bufs[1].k));
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, n, &bufs[1].v));
 
-  uint64_t* tmp_k = nullptr;
-  uint32_t* tmp_v = nullptr;
-  HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, n, &tmp_k));
-  HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, n, &tmp_v));
-
-  // look-back descriptors: tiles x 256 words, reused by every pass thanks to the epoch tag
   uint64_t* d_lb = nullptr;
-  const size_t lb_words = tiles * RADIX;
-  HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, lb_words, &d_lb));
-  if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
-      ctx->lb_epoch + NUM_PASSES >= 0xFFFF) {
-    HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
-    ctx->lb_seen_ptr = d_lb;
-    ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
-    ctx->lb_epoch = 0;
+  if (nd > 0 || finish_shift >= 0) {
+    HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, tiles * RADIX, &d_lb));
+    if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
+        ctx->lb_epoch + 3 * NUM_PASSES >= 0xFFFF) {
+      HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
+      ctx->lb_seen_ptr = d_lb;
+      ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
+      ctx->lb_epoch = 0;
+    }
   }
 
-  const bool end_in_tmp = aliased && (P & 1);
-  const uint64_t* cur_k = keys_in;
-  const uint32_t* cur_v = vals_in;
-  int j = 0;
-  for (int p = 0; p < NUM_PASSES; ++p) {
-    if (skip[p]) continue;
-    bool to_out = end_in_tmp ? (j & 1) : (((P - 1 - j) & 1) == 0);
-    uint64_t* dk = to_out ? keys_out : tmp_k;
-    uint32_t* dv = to_out ? vals_out : tmp_v;
-    const uint32_t epoch = ++ctx->lb_epoch;
-    const uint32_t* bins = d_hist + p * RADIX;
-    int rc;
-    switch (cfg) {
-      case 1: rc = launch_pass<512, 8, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
-      case 2: rc = launch_pass<256, 24, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
-      case 3: rc = launch_pass<384, 16, 2>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
-      case 4: rc = launch_pass<512, 16, 1>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
-      default: rc = launch_pass<256, 16, 3>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, d_counters + p, epoch); break;
+  int counter_idx = 0;
+  // runs scatter passes over digits[0..cnt) starting from (src_k,src_v); step j writes
+  // bufs[first_dst ^ (j & 1)].  Returns the index of the buffer holding the result.
+  auto run_passes = [&](const uint64_t* src_k, const uint32_t* src_v, const int* dg, int cnt,
+                        int first_dst, int* where) -> int {
+    const uint64_t* cur_k = src_k;
+    const uint32_t* cur_v = src_v;
+    int w = first_dst ^ 1;
+    for (int j = 0; j < cnt; ++j) {
+      w = first_dst ^ (j & 1);
+      uint64_t* dk = bufs[w].k;
+      uint32_t* dv = bufs[w].v;
+      const int p = dg[j];
+      const uint32_t epoch = ++ctx->lb_epoch;
+      const uint32_t* bins = d_hist + p * RADIX;
+      uint32_t* counter = d_counters + (counter_idx++);
+      int rc;
+#define HMJ_PASS(T, I, B, R) \
+  rc = launch_pass<T, I, B, R>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, counter, epoch)
+      switch (cfg) {
+        case 1: HMJ_PASS(512, 8, 2, 1); break;
+        case 2: HMJ_PASS(256, 24, 2, 1); break;
+        case 3: HMJ_PASS(384, 16, 2, 1); break;
+        case 4: HMJ_PASS(512, 16, 1, 1); break;
+        case 5: HMJ_PASS(256, 16, 3, 0); break;
+        case 6: HMJ_PASS(512, 12, 2, 1); break;
+        case 7: HMJ_PASS(384, 20, 1, 1); break;
+        default: HMJ_PASS(256, 16, 3, 1); break;
+      }
+#undef HMJ_PASS
+      HMJ_TRY(rc);
+      cur_k = dk;
+      cur_v = dv;
     }
-    HMJ_TRY(rc);
-    cur_k = dk;
-    cur_v = dv;
-    ++j;
+    *where = w;
+    return HMJ_OK;
+  };
+
+  // first destination chosen so that the last step lands in bufs[0]; an aliased input cannot
+  // be overwritten by the step that reads it, so it goes to the workspace first
+  int first_dst = (steps - 1) & 1;
+  if (aliased && first_dst == 0) first_dst = 1;
+  int where = first_dst ^ 1;
+  HMJ_TRY(run_passes(keys_in, vals_in, digits, nd, first_dst, &where));
+  ctx->tm.sort_passes += (uint32_t)nd;
+
+  if (finish_shift >= 0) {
+    const uint64_t* fk = nd ? bufs[where].k : keys_in;
+    const uint32_t* fv = nd ? bufs[where].v : vals_in;  // null (nd == 0 only) = iota
+    const int fdst = first_dst ^ (nd & 1);
+    bucket_finish_kernel<<<(unsigned)hmj_div_up(n, FIN_TILE), FIN_THREADS, 0, st>>>(
+        fk, fv, bufs[fdst].k, bufs[fdst].v, n32, finish_shift, d_flag);
+    HMJ_LAUNCHED(ctx);
+    ctx->tm.sort_finishes += 1;
+    uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+    if (h[0] == 0) {
+      where = fdst;
+    } else {
+      // A bucket was too large.  The finish input (the caller's input, or the prefix-sorted
+      // pairs: a stable permutation of it) is intact, so it is re-sorted from there with
+      // stable scatter passes over every non-trivial digit; the result is the same.
+      ctx->tm.sort_fallbacks += 1;
+      int all[NUM_PASSES], na = 0;
+      for (int d = 0; d < NUM_PASSES; ++d)
+        if (!trivial[d]) all[na++] = d;
+      if (na == 0) {
+        // every key is equal: the input order is the sorted order
+        HMJ_ARG(ctx, nd == 0);
+        steps = 0;
+        if (keys_in != keys_out)
+          HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
+        if (vals_in == nullptr) {
+          iota_kernel<<<(int)min(hmj_div_up(n, 256), (size_t)ctx->num_sms * 8), 256, 0, st>>>(vals_out, n32);
+          HMJ_LAUNCHED(ctx);
+        } else if (vals_in != vals_out) {
+          HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, vals_in, n * 4, cudaMemcpyDeviceToDevice, st));
+        }
+        return HMJ_OK;
+      }
+      int fd2;
+      if (nd == 0) {
+        fd2 = (na - 1) & 1;
+        if (aliased && fd2 == 0) fd2 = 1;
+      } else {
+        fd2 = where ^ 1;
+      }
+      HMJ_TRY(run_passes(fk, fv, all, na, fd2, &where));
+      ctx->tm.sort_passes += (uint32_t)na;
+    }
   }
-  if (end_in_tmp) {
-    HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, tmp_k, n * 8, cudaMemcpyDeviceToDevice, st));
-    HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, tmp_v, n * 4, cudaMemcpyDeviceToDevice, st));
+  if (where != 0) {
+    HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, bufs[1].k, n * 8, cudaMemcpyDeviceToDevice, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, bufs[1].v, n * 4, cudaMemcpyDeviceToDevice, st));
   }
   return HMJ_OK;
 }

@@ -189,6 +189,8 @@ typedef struct hmj_timings {
   /* dominant kernel (onesweep pass) timed per launch while profiling is on */
   float pass_ms_sum;     /* sum of the per-launch durations since profiling was (re)enabled */
   uint32_t pass_launches;
+  uint32_t sort_finishes;  /* bucket-finish launches (prefix sort + small-bucket finish) */
+  uint32_t sort_fallbacks; /* sorts that met an oversized bucket and re-ran with scatter passes */
 } hmj_timings;
 int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
 /* on != 0: bracket every onesweep-pass launch with CUDA events on the context's stream and

@@ -121,6 +121,81 @@ def test_sort_skips_trivial_passes_large(ctx, oracle):
     assert np.array_equal(keys[host(r, np.uint32)], np.sort(keys))
 
 
+def fast_check_sort(ctx, keys, rowid=None, inplace=False):
+    """large cases: numpy stable argsort is the check (== std::sort order of the reference tests)"""
+    keys = np.ascontiguousarray(keys, np.uint64)
+    t = dev(keys)
+    if inplace:
+        r = torch.empty(keys.size, dtype=torch.int32, device="cuda")
+        ctx.sort_pairs(t, None if rowid is None else dev(rowid), out_hash=t, out_rowid=r)
+        h = t
+    else:
+        h, r = ctx.sort_pairs(t, None if rowid is None else dev(rowid))
+    order = np.argsort(keys, kind="stable")
+    rid = np.arange(keys.size, dtype=np.uint32) if rowid is None else rowid
+    assert np.array_equal(host(h, np.uint64), keys[order])
+    assert np.array_equal(host(r, np.uint32), rid[order])
+    return ctx.timings()
+
+
+def test_sort_hybrid_prefix_and_bucket_finish(ctx):
+    # uniform keys, n >= 2^21: 3 scatter passes on the top 24 bits + bucket finish (shift 40)
+    rng = np.random.default_rng(21)
+    n = (1 << 21) + 12345
+    keys = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    f0 = ctx.timings()["sort_finishes"]
+    tm = fast_check_sort(ctx, keys)
+    assert tm["sort_finishes"] == f0 + 1, "the hybrid path did not run"
+    fast_check_sort(ctx, keys, inplace=True)
+    fast_check_sort(ctx, keys, rowid=rng.permutation(n).astype(np.uint32))
+    # every key twice: equal keys inside a bucket keep their input order
+    fast_check_sort(ctx, np.concatenate([keys[: n // 2], keys[: n // 2]]))
+    # 2^17 rows: two scatter passes, finish on shift 48
+    fast_check_sort(ctx, rng.integers(0, 2 ** 64, size=1 << 17, dtype=np.uint64))
+
+
+def test_sort_hybrid_tie_slow_path(ctx):
+    # bucket-mates that agree on the 31 bits below the 24-bit prefix and differ only in the low
+    # 9 bits: the 32-bit fast ranking cannot order them, the tile must take the full-key path
+    rng = np.random.default_rng(22)
+    n = 1 << 21
+    top = rng.integers(0, 1 << 20, size=n, dtype=np.uint64) << np.uint64(44)
+    low = rng.integers(0, 512, size=n, dtype=np.uint64)
+    tm0 = ctx.timings()
+    tm = fast_check_sort(ctx, top | low)
+    assert tm["sort_finishes"] == tm0["sort_finishes"] + 1
+    assert tm["sort_fallbacks"] == tm0["sort_fallbacks"]
+    # mixed: only some buckets tie
+    keys = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    keys[::7] = (keys[::7] & ~np.uint64((1 << 40) - 1)) | low[::7]
+    fast_check_sort(ctx, keys)
+
+
+def test_sort_hybrid_oversized_bucket_falls_back(ctx):
+    # digit histograms look uniform (1200 extra rows in a bin of 32768 is inside the planner's
+    # tolerance), but 1200 rows share one 24-bit prefix: the bucket finish flags it and the sort
+    # re-runs with scatter passes over every digit -- same result
+    rng = np.random.default_rng(23)
+    n = 1 << 23
+    keys = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    hot = rng.choice(n, size=1200, replace=False)
+    keys[hot] = (np.uint64(0xABCDEF) << np.uint64(40)) | rng.integers(0, 1 << 40, size=1200, dtype=np.uint64)
+    tm0 = ctx.timings()
+    tm = fast_check_sort(ctx, keys)
+    assert tm["sort_fallbacks"] == tm0["sort_fallbacks"] + 1
+    fast_check_sort(ctx, keys, inplace=True)
+    # 1200 copies of ONE key (a moderate heavy hitter the histogram test cannot see)
+    keys[hot] = np.uint64(0x123456789ABCDEF0)
+    fast_check_sort(ctx, keys)
+
+
+def test_sort_hybrid_small_whole_array_bucket(ctx):
+    rng = np.random.default_rng(24)
+    for n in (3, 200, 256, 257, 511, 512, 513):
+        fast_check_sort(ctx, rng.integers(0, 2 ** 64, size=n, dtype=np.uint64))
+        fast_check_sort(ctx, rng.integers(0, 5, size=n, dtype=np.uint64), inplace=True)
+
+
 def test_sort_empty(ctx):
     h, r = ctx.sort_pairs(torch.empty(0, dtype=torch.int64, device="cuda"))
     assert h.numel() == 0 and r.numel() == 0
