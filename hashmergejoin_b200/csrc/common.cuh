@@ -120,3 +120,5 @@ static inline size_t hmj_div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 // (implemented in hash.cu / radix_sort.cu / merge_join.cu / hash_table.cu / partition.cu)
 int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* d_keys_in, const uint32_t* d_vals_in, size_t n,
                   uint64_t* d_keys_out, uint32_t* d_vals_out);
+int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+                         uint64_t* h_num_pairs);

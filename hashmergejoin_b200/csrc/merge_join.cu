@@ -25,9 +25,9 @@ namespace {
 
 constexpr int JOIN_THREADS = 256;
 constexpr int JOIN_TILE = 4096;  // merged elements per tile
-constexpr size_t JOIN_SMEM = (size_t)JOIN_TILE * 8 + (size_t)JOIN_TILE * 4 + 256;
+constexpr size_t JOIN_SMEM = (size_t)JOIN_TILE * 8 + (size_t)JOIN_TILE * 4 * 2 + 8192;
 
-enum JoinMode { JOIN_COUNT = 0, JOIN_WRITE = 1, JOIN_AGG = 2 };
+enum JoinMode { JOIN_COUNT = 0, JOIN_WRITE = 1, JOIN_AGG = 2, JOIN_FUSED = 3 };
 
 struct JoinArgs {
   const uint64_t* rh;
@@ -49,7 +49,10 @@ struct JoinArgs {
   const uint64_t* tile_offset; // [tiles] exclusive scan (write mode reads)
   uint32_t* out_r;
   uint32_t* out_s;
-  uint64_t* agg;               // [2]: pairs, sum
+  uint64_t* agg;               // [0],[1]: pairs, sum (aggregate); [2]: total pairs
+  uint64_t* tile_desc;         // [tiles] look-back descriptors (fused mode)
+  uint32_t* tile_counter;      // dynamic tile ids (fused mode)
+  uint64_t cap;                // capacity of out_r/out_s in pairs (fused mode)
   uint32_t tiles;
 };
 
@@ -170,17 +173,126 @@ __device__ __forceinline__ uint64_t block_excl_scan_u64(uint64_t v, uint64_t* s_
   return pre + x - v;
 }
 
+// ---- cooperative handling of long runs -------------------------------------------------
+// A probe (R) element whose equal-hash run in S is longer than JOIN_BIG is not walked by its
+// own thread: the owner parks its parameters in shared memory and the whole CTA walks the run
+// with coalesced accesses (counting verified candidates, or emitting pairs).
+constexpr int JOIN_BIG = 64;
+
+struct JoinShared {  // lives behind the tile arrays in dynamic shared memory
+  uint64_t tmp[JOIN_THREADS / 32 + 2];
+  uint64_t p_off[JOIN_THREADS];
+  uint32_t p_rrow[JOIN_THREADS], p_lb[JOIN_THREADS], p_n[JOIN_THREADS], p_res[JOIN_THREADS];
+  uint32_t q[JOIN_THREADS];
+  uint32_t qn;
+  uint32_t tile;
+  uint64_t base;
+};
+
+template <int KIND>
+__device__ __forceinline__ bool cand_ok(const JoinArgs& A, uint32_t rrow, uint32_t srow) {
+  if (KIND == HMJ_KEY_U64) return true;
+  return keys_equal_str(A.roff, A.rchars, rrow, A.soff, A.schars, srow);
+}
+
+// all threads: verified candidates of every queued run -> p_res[owner]
+template <int KIND>
+__device__ void coop_count(const JoinArgs& A, JoinShared* sh) {
+  __syncthreads();
+  const uint32_t qn = sh->qn;
+  for (uint32_t e = 0; e < qn; ++e) {
+    const uint32_t o = sh->q[e];
+    const uint32_t rrow = sh->p_rrow[o], lb = sh->p_lb[o], n = sh->p_n[o];
+    uint64_t c = 0;
+    for (uint32_t t = threadIdx.x; t < n; t += JOIN_THREADS)
+      c += cand_ok<KIND>(A, rrow, A.sr[lb + t]) ? 1 : 0;
+    const uint64_t tot = block_reduce_u64(c, sh->tmp);
+    if (threadIdx.x == 0) sh->p_res[o] = (uint32_t)tot;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) sh->qn = 0;
+  __syncthreads();
+}
+
+// all threads: emit (or aggregate) the pairs of every queued run
+template <int KIND, int MODE>
+__device__ void coop_emit(const JoinArgs& A, JoinShared* sh, bool do_write, uint64_t* my_sum) {
+  __syncthreads();
+  const uint32_t qn = sh->qn;
+  for (uint32_t e = 0; e < qn; ++e) {
+    const uint32_t o = sh->q[e];
+    const uint32_t rrow = sh->p_rrow[o], lb = sh->p_lb[o], n = sh->p_n[o];
+    uint64_t off = sh->p_off[o];
+    const uint64_t rv = (MODE == JOIN_AGG) ? (A.rvals ? A.rvals[rrow] : (uint64_t)rrow) : 0;
+    for (uint32_t c0 = 0; c0 < n; c0 += JOIN_THREADS) {
+      const uint32_t t = c0 + threadIdx.x;
+      uint32_t srow = 0;
+      bool ok = false;
+      if (t < n) {
+        srow = A.sr[lb + t];
+        ok = cand_ok<KIND>(A, rrow, srow);
+      }
+      if (MODE == JOIN_AGG) {
+        if (ok) *my_sum += rv + (A.svals ? A.svals[srow] : (uint64_t)srow);
+      } else if (KIND == HMJ_KEY_U64) {
+        if (ok && do_write) {
+          A.out_r[off + t] = rrow;
+          A.out_s[off + t] = srow;
+        }
+      } else {
+        uint64_t tot;
+        const uint64_t pre = block_excl_scan_u64(ok ? 1 : 0, sh->tmp, &tot);
+        if (ok && do_write) {
+          A.out_r[off + pre] = rrow;
+          A.out_s[off + pre] = srow;
+        }
+        off += tot;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) sh->qn = 0;
+  __syncthreads();
+}
+
+static_assert(sizeof(JoinShared) <= 8192, "JOIN_SMEM reserves 8 KB for JoinShared");
+constexpr uint64_t JD_PARTIAL = 1ull << 62;
+constexpr uint64_t JD_INCLUSIVE = 2ull << 62;
+constexpr uint64_t JD_VALUE = (1ull << 62) - 1;
+
+__device__ __forceinline__ void jd_store(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t jd_load(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// One tile of the merged order.  MODE:
+//   JOIN_COUNT : per-tile match counts (tile_counts) only
+//   JOIN_WRITE : offsets known (tile_offset, after join_scan_kernel): write the pairs
+//   JOIN_AGG   : count + sum of payloads, nothing materialised
+//   JOIN_FUSED : single pass -- count the tile, obtain its output offset by a decoupled look-back
+//                over per-tile descriptors, write the pairs if they fit in `cap`; tile_counts are
+//                published too, so an overflowing join can finish with scan + JOIN_WRITE.
 template <int KIND, int MODE>
 __global__ void __launch_bounds__(JOIN_THREADS)
 join_tile_kernel(const JoinArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s_h = reinterpret_cast<uint64_t*>(smem_raw);           // [T] R hashes then S hashes
   uint32_t* s_id = reinterpret_cast<uint32_t*>(s_h + JOIN_TILE);   // [T] row ids, same order
-  uint64_t* s_tmp = reinterpret_cast<uint64_t*>(s_id + JOIN_TILE); // [8+] scan scratch
+  uint32_t* s_cnt = s_id + JOIN_TILE;                              // [T] FUSED: matches per R element
+  JoinShared* sh = reinterpret_cast<JoinShared*>(s_cnt + JOIN_TILE);
   constexpr bool NEED_IDS = (KIND == HMJ_KEY_STRING) || (MODE != JOIN_COUNT);
-
-  const uint32_t tile = blockIdx.x;
   const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    sh->qn = 0;
+    sh->tile = (MODE == JOIN_FUSED) ? atomicAdd(A.tile_counter, 1u) : blockIdx.x;
+  }
+  __syncthreads();
+  const uint32_t tile = sh->tile;
   const uint64_t total = (uint64_t)A.nr + A.ns;
   const uint64_t d0 = min((uint64_t)tile * JOIN_TILE, total);
   const uint64_t d1 = min((uint64_t)(tile + 1) * JOIN_TILE, total);
@@ -202,69 +314,140 @@ join_tile_kernel(const JoinArgs A) {
 
   uint64_t my_pairs = 0, my_sum = 0;
   uint64_t running = (MODE == JOIN_WRITE) ? A.tile_offset[tile] : 0;
+  bool do_write = (MODE == JOIN_WRITE);
+  const uint32_t rounds = (na + JOIN_THREADS - 1) / JOIN_THREADS;
 
-  for (uint32_t base = 0; base < na; base += JOIN_THREADS) {
-    const uint32_t li = base + tid;
+  // emits the pairs of one round: per-thread (rrow, lb, ncand, cnt), offsets from a block scan
+  auto emit_round = [&](bool active, uint32_t rrow, uint32_t lb, uint32_t ncand, uint32_t cnt,
+                        uint64_t vmask, bool have_mask) {
+    uint64_t off = 0;
+    if (MODE != JOIN_AGG) {
+      uint64_t round_total;
+      off = running + block_excl_scan_u64(cnt, sh->tmp, &round_total);
+      running += round_total;
+    }
+    const bool big = active && ncand > (uint32_t)JOIN_BIG;
+    if (big) {
+      sh->p_rrow[tid] = rrow; sh->p_lb[tid] = lb; sh->p_n[tid] = ncand; sh->p_off[tid] = off;
+      sh->q[atomicAdd(&sh->qn, 1u)] = tid;
+    } else if (active && cnt && (do_write || MODE == JOIN_AGG)) {
+      const uint64_t rv = (MODE == JOIN_AGG) ? (A.rvals ? A.rvals[rrow] : (uint64_t)rrow) : 0;
+      for (uint32_t t = 0; t < ncand; ++t) {
+        const uint32_t j = lb + t;
+        const uint32_t srow = (j >= b0 && j < b1) ? s_ids[j - b0] : A.sr[j];
+        if (KIND == HMJ_KEY_STRING) {
+          const bool ok = (have_mask && t < 64) ? ((vmask >> t) & 1) : cand_ok<KIND>(A, rrow, srow);
+          if (!ok) continue;
+        }
+        if (MODE == JOIN_AGG) {
+          my_sum += rv + (A.svals ? A.svals[srow] : (uint64_t)srow);
+        } else {
+          A.out_r[off] = rrow;
+          A.out_s[off] = srow;
+          ++off;
+        }
+      }
+    }
+    if (__syncthreads_or(big)) coop_emit<KIND, MODE>(A, sh, do_write, &my_sum);
+  };
+
+  // ---- phase A: equal-hash run of every R element, verified match count
+  for (uint32_t r = 0; r < rounds; ++r) {
+    const uint32_t li = r * JOIN_THREADS + tid;
     const bool active = li < na;
-    uint32_t lb = 0, ub = 0, cnt = 0, rrow = 0;
+    uint32_t lb = 0, ncand = 0, cnt = 0, rrow = 0;
     uint64_t vmask = 0;  // verified-candidate bitmap of the first 64 candidates (strings)
+    bool big = false;
     if (active) {
       const uint64_t h = s_h[li];
       const uint32_t l = lower_bound_dev(s_hs, 0u, nb, h);
       const uint32_t u = upper_bound_dev(s_hs, l, nb, h);
       lb = b0 + l;
-      ub = (u == nb) ? gallop_upper(A.sh, b1, A.ns, h) : b0 + u;
+      const uint32_t ub = (u == nb) ? gallop_upper(A.sh, b1, A.ns, h) : b0 + u;
+      ncand = ub - lb;
       if (NEED_IDS) rrow = s_id[li];
       if (KIND == HMJ_KEY_U64) {
-        cnt = ub - lb;
+        cnt = ncand;
+      } else if (ncand > (uint32_t)JOIN_BIG) {
+        big = true;
+        sh->p_rrow[tid] = rrow; sh->p_lb[tid] = lb; sh->p_n[tid] = ncand;
+        sh->q[atomicAdd(&sh->qn, 1u)] = tid;
       } else {
-        for (uint32_t j = lb; j < ub; ++j) {
+        for (uint32_t t = 0; t < ncand; ++t) {
+          const uint32_t j = lb + t;
           const uint32_t srow = (j < b1) ? s_ids[j - b0] : A.sr[j];
-          if (keys_equal_str(A.roff, A.rchars, rrow, A.soff, A.schars, srow)) {
-            if (j - lb < 64) vmask |= 1ull << (j - lb);
+          if (cand_ok<KIND>(A, rrow, srow)) {
+            vmask |= 1ull << t;
             ++cnt;
           }
         }
       }
     }
-    if (MODE == JOIN_COUNT) {
-      my_pairs += cnt;
-    } else {
-      uint64_t off = 0;
-      if (MODE == JOIN_WRITE) {
-        uint64_t round_total;
-        off = running + block_excl_scan_u64(cnt, s_tmp, &round_total);
-        running += round_total;
-      }
-      if (active && cnt) {
-        uint64_t rv = 0;
-        if (MODE == JOIN_AGG) rv = A.rvals ? A.rvals[rrow] : (uint64_t)rrow;
-        for (uint32_t j = lb; j < ub; ++j) {
-          const uint32_t srow = (j < b1) ? s_ids[j - b0] : A.sr[j];
-          if (KIND == HMJ_KEY_STRING) {
-            const bool ok = (j - lb < 64)
-                                ? ((vmask >> (j - lb)) & 1)
-                                : keys_equal_str(A.roff, A.rchars, rrow, A.soff, A.schars, srow);
-            if (!ok) continue;
-          }
-          if (MODE == JOIN_WRITE) {
-            A.out_r[off] = rrow;
-            A.out_s[off] = srow;
-            ++off;
-          } else {
-            my_sum += rv + (A.svals ? A.svals[srow] : (uint64_t)srow);
-          }
-        }
-        my_pairs += cnt;
+    if (KIND == HMJ_KEY_STRING) {
+      if (__syncthreads_or(big)) {
+        coop_count<KIND>(A, sh);
+        if (big) cnt = sh->p_res[tid];
       }
     }
+    my_pairs += cnt;
+    if (MODE == JOIN_WRITE || MODE == JOIN_AGG) {
+      emit_round(active, rrow, lb, ncand, cnt, vmask, true);
+    } else if (MODE == JOIN_FUSED && active) {
+      s_h[li] = (uint64_t)lb | ((uint64_t)ncand << 32);
+      s_cnt[li] = cnt;
+    }
   }
-  if (MODE == JOIN_COUNT) {
-    const uint64_t t = block_reduce_u64(my_pairs, s_tmp);
-    if (tid == 0) A.tile_counts[tile] = t;
+
+  if (MODE == JOIN_COUNT || MODE == JOIN_FUSED) {
+    const uint64_t t = block_reduce_u64(my_pairs, sh->tmp);
+    if (tid == 0) {
+      A.tile_counts[tile] = t;
+      if (MODE == JOIN_FUSED) {
+        // decoupled look-back over the tiles before this one
+        uint64_t excl = 0;
+        if (tile != 0) {
+          jd_store(A.tile_desc + tile, JD_PARTIAL | t);
+          int64_t prev = (int64_t)tile - 1;
+          while (true) {
+            const uint64_t v = jd_load(A.tile_desc + prev);
+            if ((v >> 62) == 0) continue;
+            excl += v & JD_VALUE;
+            if ((v >> 62) == 2) break;
+            --prev;
+          }
+        }
+        jd_store(A.tile_desc + tile, JD_INCLUSIVE | (excl + t));
+        if (tile == A.tiles - 1) A.agg[2] = excl + t;
+        sh->base = excl;
+        sh->p_off[0] = t;
+      }
+    }
+    if (MODE == JOIN_FUSED) {
+      __syncthreads();
+      running = sh->base;
+      const uint64_t tile_total = sh->p_off[0];
+      do_write = running + tile_total <= A.cap;
+      __syncthreads();
+      if (tile_total != 0 && do_write) {
+        // ---- phase B: emit with the offsets now known
+        for (uint32_t r = 0; r < rounds; ++r) {
+          const uint32_t li = r * JOIN_THREADS + tid;
+          const bool active = li < na;
+          uint32_t lb = 0, ncand = 0, cnt = 0, rrow = 0;
+          if (active) {
+            const uint64_t w = s_h[li];
+            lb = (uint32_t)w;
+            ncand = (uint32_t)(w >> 32);
+            cnt = s_cnt[li];
+            rrow = s_id[li];
+          }
+          emit_round(active, rrow, lb, ncand, cnt, 0, false);
+        }
+      }
+    }
   } else if (MODE == JOIN_AGG) {
-    const uint64_t p = block_reduce_u64(my_pairs, s_tmp);
-    const uint64_t s = block_reduce_u64(my_sum, s_tmp);
+    const uint64_t p = block_reduce_u64(my_pairs, sh->tmp);
+    const uint64_t s = block_reduce_u64(my_sum, sh->tmp);
     if (tid == 0) {
       if (p) atomicAdd(reinterpret_cast<unsigned long long*>(A.agg), (unsigned long long)p);
       if (s) atomicAdd(reinterpret_cast<unsigned long long*>(A.agg + 1), (unsigned long long)s);
@@ -337,14 +520,17 @@ int join_plan(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s, JoinPl
   const uint64_t total = (uint64_t)r->n + s->n;
   A.tiles = (uint32_t)hmj_div_up(total, JOIN_TILE);
   uint32_t* tile_a = nullptr;
-  // layout of WS_JOIN_TILES: [tiles+1] u32 tile_a | [tiles] u64 counts | [tiles] u64 offsets
+  // layout of WS_JOIN_TILES: [tiles+1] u32 tile_a | [tiles] u64 counts | [tiles] u64 offsets |
+  // [tiles] u64 look-back descriptors | u32 tile counter
   const size_t a_bytes = (((size_t)A.tiles + 1) * 4 + 15) & ~size_t(15);
   void* base = nullptr;
-  HMJ_TRY(hmj_ws_get(ctx, WS_JOIN_TILES, a_bytes + (size_t)A.tiles * 16 + 16, &base));
+  HMJ_TRY(hmj_ws_get(ctx, WS_JOIN_TILES, a_bytes + (size_t)A.tiles * 24 + 32, &base));
   tile_a = reinterpret_cast<uint32_t*>(base);
   A.tile_a = tile_a;
   A.tile_counts = reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(base) + a_bytes);
   A.tile_offset = A.tile_counts + A.tiles;
+  A.tile_desc = const_cast<uint64_t*>(A.tile_offset) + A.tiles;
+  A.tile_counter = reinterpret_cast<uint32_t*>(A.tile_desc + A.tiles);
   uint64_t* scal = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_SCALARS, 8, &scal));
   A.agg = scal;  // [0],[1] aggregate; [2] scan total
@@ -388,7 +574,56 @@ int join_count(hmj_ctx* ctx, JoinPlan* plan, uint64_t* h_total) {
   return HMJ_OK;
 }
 
+// Fused count + write in one pass over the tiles; pairs are written only while they fit in
+// `cap`.  Returns the exact total; when it exceeds cap nothing useful was written and the
+// caller re-runs with a larger buffer (tile_counts are valid: scan + JOIN_WRITE would do too).
+int join_fused(hmj_ctx* ctx, JoinPlan* plan, uint32_t* d_out_r, uint32_t* d_out_s, uint64_t cap,
+               uint64_t* h_total) {
+  *h_total = 0;
+  JoinArgs& A = plan->args;
+  if (A.tiles == 0) return HMJ_OK;
+  A.out_r = d_out_r;
+  A.out_s = d_out_s;
+  A.cap = cap;
+  HMJ_CUDA(ctx, cudaMemsetAsync(A.tile_desc, 0, (size_t)A.tiles * 8 + 16, ctx->stream));
+  HMJ_TRY(launch_tiles<JOIN_FUSED>(ctx, *plan));
+  uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.agg + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *h_total = h[0];
+  return HMJ_OK;
+}
+
 }  // namespace
+
+// whole-operator helper (operator.cu): join two sorted relations into the context's result
+// buffers, growing them when the first (optimistic) capacity was too small.
+int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+                         uint64_t* h_num_pairs) {
+  JoinPlan plan;
+  HMJ_TRY(join_plan(ctx, r, s, &plan));
+  // optimistic capacity: what the buffers already hold, at least max(|R|,|S|) pairs
+  size_t cap = ctx->ws[WS_OUT_R].bytes / 4;
+  const size_t guess = r->n > s->n ? r->n : s->n;
+  if (cap < guess) cap = guess;
+  uint32_t *out_r = nullptr, *out_s = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_R, cap, &out_r));
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_S, cap, &out_s));
+  cap = ctx->ws[WS_OUT_R].bytes / 4;
+  if (ctx->ws[WS_OUT_S].bytes / 4 < cap) cap = ctx->ws[WS_OUT_S].bytes / 4;
+  uint64_t m = 0;
+  HMJ_TRY(join_fused(ctx, &plan, out_r, out_s, cap, &m));
+  if (m > cap) {
+    HMJ_TRY(hmj_ws(ctx, WS_OUT_R, (size_t)m, &out_r));
+    HMJ_TRY(hmj_ws(ctx, WS_OUT_S, (size_t)m, &out_s));
+    uint64_t m2 = 0;
+    HMJ_TRY(join_fused(ctx, &plan, out_r, out_s, m, &m2));
+    m = m2;
+  }
+  ctx->last_pairs = m;
+  *h_num_pairs = m;
+  return HMJ_OK;
+}
 
 extern "C" int hmj_merge_join_count(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
                                     uint64_t* h_num_pairs) {
@@ -404,16 +639,13 @@ extern "C" int hmj_merge_join_write(hmj_ctx* ctx, const hmj_relation* r, const h
                                     uint64_t* h_num_pairs) {
   if (!ctx) return HMJ_EARG;
   HMJ_ARG(ctx, h_num_pairs != nullptr);
+  HMJ_ARG(ctx, cap == 0 || (d_out_r && d_out_s));
   JoinPlan plan;
   HMJ_TRY(join_plan(ctx, r, s, &plan));
-  HMJ_TRY(join_count(ctx, &plan, h_num_pairs));
+  HMJ_TRY(join_fused(ctx, &plan, d_out_r, d_out_s, cap, h_num_pairs));
   if (*h_num_pairs > cap)
     return hmj_fail(ctx, HMJ_ECAPACITY, "output capacity too small", __FILE__, __LINE__);
-  if (*h_num_pairs == 0) return HMJ_OK;
-  HMJ_ARG(ctx, d_out_r && d_out_s);
-  plan.args.out_r = d_out_r;
-  plan.args.out_s = d_out_s;
-  return launch_tiles<JOIN_WRITE>(ctx, plan);
+  return HMJ_OK;
 }
 
 extern "C" int hmj_merge_join_aggregate(hmj_ctx* ctx, const hmj_relation* r,

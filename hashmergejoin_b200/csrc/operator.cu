@@ -17,17 +17,7 @@ int sort_side_u64(hmj_ctx* ctx, const uint64_t* d_keys, size_t n, int slot_h, in
 }
 
 int join_sorted(hmj_ctx* ctx, const hmj_relation* R, const hmj_relation* S, uint64_t* h_num_pairs) {
-  uint64_t m = 0;
-  HMJ_TRY(hmj_merge_join_count(ctx, R, S, &m));
-  uint32_t *out_r = nullptr, *out_s = nullptr;
-  HMJ_TRY(hmj_ws(ctx, WS_OUT_R, (size_t)m, &out_r));
-  HMJ_TRY(hmj_ws(ctx, WS_OUT_S, (size_t)m, &out_s));
-  uint64_t m2 = 0;
-  // TODO(perf): reuse the count pass's tile offsets instead of recounting inside write
-  HMJ_TRY(hmj_merge_join_write(ctx, R, S, out_r, out_s, (size_t)m, &m2));
-  ctx->last_pairs = m2;
-  *h_num_pairs = m2;
-  return HMJ_OK;
+  return hmj_impl_join_sorted(ctx, R, S, h_num_pairs);
 }
 
 }  // namespace

@@ -166,18 +166,26 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
   for (int k = 0; k < ITEMS; ++k) {
     const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
     uint32_t peers;
-    if (RANK_MODE == 0) {
-      // MATCH.ANY runs on the ADU pipe (about 65 cycles per warp instruction per SM measured,
-      // profiles/r1a_*): kept only for comparison
+    // RANK_MODE = how many of every 4 items use MATCH.ANY (ADU pipe, ~65 cycles per warp
+    // instruction per SM, profiles/r1a_*); the rest use one ballot per digit bit (ALU pipe).
+    // Mixing keeps both pipes busy.  4 = all MATCH (round-1a kernel), 0 = all ballots.
+    if ((k & 3) < RANK_MODE) {
       peers = __match_any_sync(0xffffffffu, d);
     } else {
-      // one ballot per digit bit: lanes whose digit agrees with mine on every bit
       peers = 0xffffffffu;
 #pragma unroll
       for (int b = 0; b < RADIX_BITS; ++b) {
-        const bool bit = (d >> b) & 1u;
-        const uint32_t m = __ballot_sync(0xffffffffu, bit);
-        peers &= bit ? m : ~m;
+        asm("{\n\t"
+            ".reg .pred p;\n\t"
+            ".reg .b32 m;\n\t"
+            "and.b32 m, %1, %2;\n\t"
+            "setp.ne.u32 p, m, 0;\n\t"
+            "vote.sync.ballot.b32 m, p, 0xffffffff;\n\t"
+            "@!p not.b32 m, m;\n\t"
+            "and.b32 %0, %0, m;\n\t"
+            "}"
+            : "+r"(peers)
+            : "r"(d), "r"(1u << b));
       }
     }
     const int leader = __ffs(peers) - 1;
@@ -280,7 +288,7 @@ __global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = i;
 }
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE = 1>
+template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE = 0>
 int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
                 uint32_t* vout, uint32_t n, int shift, const uint32_t* bins, uint64_t* lookback,
                 uint32_t* counter, uint32_t epoch, uint32_t iota_base = 0) {
@@ -318,13 +326,8 @@ int sort_cfg_from_env() {
 
 int tile_items_for_cfg(int cfg) {
   switch (cfg) {
-    case 1: return OnesweepCfg<512, 8>::TILE;
-    case 2: return OnesweepCfg<256, 24>::TILE;
-    case 3: return OnesweepCfg<384, 16>::TILE;
-    case 4: return OnesweepCfg<512, 16>::TILE;
-    case 5: return OnesweepCfg<256, 16>::TILE;  // MATCH.ANY ranking (round-1a kernel)
-    case 6: return OnesweepCfg<512, 12>::TILE;
-    case 7: return OnesweepCfg<384, 20>::TILE;
+    case 3: case 8: case 9: return OnesweepCfg<384, 16>::TILE;
+    case 4: case 6: case 7: return OnesweepCfg<256, 24>::TILE;
     default: return OnesweepCfg<256, 16>::TILE;
   }
 }
@@ -534,7 +537,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   bool hybrid = hybrid_from_env() != 0 && (planned || n <= (size_t)FIN_MAX_BUCKET);
   if (hybrid) {
     // include top digits until the prefix separates the keys into buckets of <= ~16..32
-    const double need = n <= (size_t)FIN_MAX_BUCKET / 2 ? 0.0 : floor(log2((double)n)) - 4.0;
+    const double need = n <= (size_t)FIN_MAX_BUCKET / 2 ? 0.0 : floor(log2((double)n)) - 3.0;
     double eff = 0;
     int q = 0, nontrivial = 0;
     bool skewed = false;
@@ -613,14 +616,16 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
 #define HMJ_PASS(T, I, B, R) \
   rc = launch_pass<T, I, B, R>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, counter, epoch)
       switch (cfg) {
-        case 1: HMJ_PASS(512, 8, 2, 1); break;
-        case 2: HMJ_PASS(256, 24, 2, 1); break;
-        case 3: HMJ_PASS(384, 16, 2, 1); break;
-        case 4: HMJ_PASS(512, 16, 1, 1); break;
-        case 5: HMJ_PASS(256, 16, 3, 0); break;
-        case 6: HMJ_PASS(512, 12, 2, 1); break;
-        case 7: HMJ_PASS(384, 20, 1, 1); break;
-        default: HMJ_PASS(256, 16, 3, 1); break;
+        case 1: HMJ_PASS(256, 16, 3, 1); break;
+        case 2: HMJ_PASS(256, 16, 3, 2); break;
+        case 3: HMJ_PASS(384, 16, 2, 0); break;
+        case 4: HMJ_PASS(256, 24, 2, 0); break;
+        case 5: HMJ_PASS(256, 16, 3, 4); break;
+        case 6: HMJ_PASS(256, 24, 2, 1); break;
+        case 7: HMJ_PASS(256, 24, 2, 2); break;
+        case 8: HMJ_PASS(384, 16, 2, 1); break;
+        case 9: HMJ_PASS(384, 16, 2, 2); break;
+        default: HMJ_PASS(256, 16, 3, 0); break;
       }
 #undef HMJ_PASS
       HMJ_TRY(rc);
