@@ -25,7 +25,13 @@ namespace {
 
 constexpr int JOIN_THREADS = 256;
 constexpr int JOIN_TILE = 4096;  // merged elements per tile
-constexpr size_t JOIN_SMEM = (size_t)JOIN_TILE * 8 + (size_t)JOIN_TILE * 4 * 2 + 8192;
+constexpr int JOIN_VT = JOIN_TILE / JOIN_THREADS;  // merged elements per thread in the tile merge
+// hashes are stored padded (one extra slot per 8) so that threads walking their own chunk of the
+// merged order (stride ~8 per array) hit different banks
+__host__ __device__ constexpr uint32_t jpad(uint32_t i) { return i + (i >> 3); }
+constexpr size_t JOIN_HASH_SLOTS = JOIN_TILE + JOIN_TILE / 8 + 2;
+constexpr size_t JOIN_SMEM_BASE = JOIN_HASH_SLOTS * 8 + (size_t)JOIN_TILE * 4 + (size_t)JOIN_TILE * 2 + 8192;
+constexpr size_t JOIN_SMEM_STR = JOIN_SMEM_BASE + (size_t)JOIN_TILE * 4;  // + verified counts
 
 enum JoinMode { JOIN_COUNT = 0, JOIN_WRITE = 1, JOIN_AGG = 2, JOIN_FUSED = 3 };
 
@@ -280,10 +286,11 @@ template <int KIND, int MODE>
 __global__ void __launch_bounds__(JOIN_THREADS)
 join_tile_kernel(const JoinArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  uint64_t* s_h = reinterpret_cast<uint64_t*>(smem_raw);           // [T] R hashes then S hashes
-  uint32_t* s_id = reinterpret_cast<uint32_t*>(s_h + JOIN_TILE);   // [T] row ids, same order
-  uint32_t* s_cnt = s_id + JOIN_TILE;                              // [T] FUSED: matches per R element
-  JoinShared* sh = reinterpret_cast<JoinShared*>(s_cnt + JOIN_TILE);
+  uint64_t* s_h = reinterpret_cast<uint64_t*>(smem_raw);               // R hashes then S hashes, padded
+  uint32_t* s_id = reinterpret_cast<uint32_t*>(s_h + JOIN_HASH_SLOTS); // [T] row ids, same order
+  uint16_t* s_lb = reinterpret_cast<uint16_t*>(s_id + JOIN_TILE);      // [T] lower bound in the S span
+  JoinShared* sh = reinterpret_cast<JoinShared*>(s_lb + JOIN_TILE);
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(sh) + 8192);  // strings
   constexpr bool NEED_IDS = (KIND == HMJ_KEY_STRING) || (MODE != JOIN_COUNT);
   const int tid = threadIdx.x;
 
@@ -300,17 +307,48 @@ join_tile_kernel(const JoinArgs A) {
   const uint32_t b0 = (uint32_t)(d0 - a0), b1 = (uint32_t)(d1 - a1);
   const uint32_t na = a1 - a0, nb = b1 - b0;
 
+  // R hashes at padded slots [0,na), S hashes at padded slots of (na + i)
   for (uint32_t i = tid; i < na; i += JOIN_THREADS) {
-    s_h[i] = __ldcs(A.rh + a0 + i);
+    s_h[jpad(i)] = __ldcs(A.rh + a0 + i);
     if (NEED_IDS) s_id[i] = __ldcs(A.rr + a0 + i);
   }
   for (uint32_t i = tid; i < nb; i += JOIN_THREADS) {
-    s_h[na + i] = __ldcs(A.sh + b0 + i);
+    s_h[jpad(na + i)] = __ldcs(A.sh + b0 + i);
     if (NEED_IDS) s_id[na + i] = __ldcs(A.sr + b0 + i);
   }
   __syncthreads();
-  const uint64_t* s_hs = s_h + na;
   const uint32_t* s_ids = s_id + na;
+  auto RH = [&](uint32_t i) -> uint64_t { return s_h[jpad(i)]; };
+  auto SH = [&](uint32_t i) -> uint64_t { return s_h[jpad(na + i)]; };
+
+  // ---- tile merge: every thread walks JOIN_VT consecutive elements of the merged order (ties:
+  // R first) and records, for each R element it passes, how many S elements precede it = the
+  // lower bound of its hash in the S span.
+  {
+    const uint32_t nt = na + nb;
+    const uint32_t diag = min((uint32_t)tid * JOIN_VT, nt);
+    uint32_t lo = diag > nb ? diag - nb : 0, hi = min(diag, na);
+    while (lo < hi) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (RH(mid) <= SH(diag - 1 - mid)) lo = mid + 1; else hi = mid;
+    }
+    uint32_t a = lo, b = diag - lo;
+    uint64_t ra = a < na ? RH(a) : 0, sb = b < nb ? SH(b) : 0;
+#pragma unroll 4
+    for (int i = 0; i < JOIN_VT; ++i) {
+      if (a + b >= nt) break;
+      const bool take_r = (b >= nb) || (a < na && ra <= sb);
+      if (take_r) {
+        s_lb[a] = (uint16_t)b;
+        ++a;
+        if (a < na) ra = RH(a);
+      } else {
+        ++b;
+        if (b < nb) sb = SH(b);
+      }
+    }
+  }
+  __syncthreads();
 
   uint64_t my_pairs = 0, my_sum = 0;
   uint64_t running = (MODE == JOIN_WRITE) ? A.tile_offset[tile] : 0;
@@ -359,9 +397,19 @@ join_tile_kernel(const JoinArgs A) {
     uint64_t vmask = 0;  // verified-candidate bitmap of the first 64 candidates (strings)
     bool big = false;
     if (active) {
-      const uint64_t h = s_h[li];
-      const uint32_t l = lower_bound_dev(s_hs, 0u, nb, h);
-      const uint32_t u = upper_bound_dev(s_hs, l, nb, h);
+      const uint64_t h = RH(li);
+      const uint32_t l = s_lb[li];
+      // upper bound: short runs by stepping, longer ones by bisection in the S span
+      uint32_t u = l;
+      while (u < nb && u < l + 4 && SH(u) == h) ++u;
+      if (u == l + 4 && u < nb && SH(u) == h) {
+        uint32_t lo2 = u + 1, hi2 = nb;
+        while (lo2 < hi2) {
+          const uint32_t mid = lo2 + ((hi2 - lo2) >> 1);
+          if (SH(mid) <= h) lo2 = mid + 1; else hi2 = mid;
+        }
+        u = lo2;
+      }
       lb = b0 + l;
       const uint32_t ub = (u == nb) ? gallop_upper(A.sh, b1, A.ns, h) : b0 + u;
       ncand = ub - lb;
@@ -393,8 +441,9 @@ join_tile_kernel(const JoinArgs A) {
     if (MODE == JOIN_WRITE || MODE == JOIN_AGG) {
       emit_round(active, rrow, lb, ncand, cnt, vmask, true);
     } else if (MODE == JOIN_FUSED && active) {
-      s_h[li] = (uint64_t)lb | ((uint64_t)ncand << 32);
-      s_cnt[li] = cnt;
+      // this thread alone reads R hash li from here on: reuse its slot for (lb, ncand)
+      s_h[jpad(li)] = (uint64_t)lb | ((uint64_t)ncand << 32);
+      if (KIND == HMJ_KEY_STRING) s_cnt[li] = cnt;
     }
   }
 
@@ -435,10 +484,10 @@ join_tile_kernel(const JoinArgs A) {
           const bool active = li < na;
           uint32_t lb = 0, ncand = 0, cnt = 0, rrow = 0;
           if (active) {
-            const uint64_t w = s_h[li];
+            const uint64_t w = s_h[jpad(li)];
             lb = (uint32_t)w;
             ncand = (uint32_t)(w >> 32);
-            cnt = s_cnt[li];
+            cnt = (KIND == HMJ_KEY_STRING) ? s_cnt[li] : ncand;
             rrow = s_id[li];
           }
           emit_round(active, rrow, lb, ncand, cnt, 0, false);
@@ -547,12 +596,12 @@ int launch_tiles(hmj_ctx* ctx, const JoinPlan& plan) {
   if (plan.args.tiles == 0) return HMJ_OK;
   if (plan.kind == HMJ_KEY_U64) {
     HMJ_CUDA(ctx, cudaFuncSetAttribute(join_tile_kernel<HMJ_KEY_U64, MODE>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JOIN_SMEM));
-    join_tile_kernel<HMJ_KEY_U64, MODE><<<plan.args.tiles, JOIN_THREADS, JOIN_SMEM, ctx->stream>>>(plan.args);
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JOIN_SMEM_BASE));
+    join_tile_kernel<HMJ_KEY_U64, MODE><<<plan.args.tiles, JOIN_THREADS, JOIN_SMEM_BASE, ctx->stream>>>(plan.args);
   } else {
     HMJ_CUDA(ctx, cudaFuncSetAttribute(join_tile_kernel<HMJ_KEY_STRING, MODE>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JOIN_SMEM));
-    join_tile_kernel<HMJ_KEY_STRING, MODE><<<plan.args.tiles, JOIN_THREADS, JOIN_SMEM, ctx->stream>>>(plan.args);
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JOIN_SMEM_STR));
+    join_tile_kernel<HMJ_KEY_STRING, MODE><<<plan.args.tiles, JOIN_THREADS, JOIN_SMEM_STR, ctx->stream>>>(plan.args);
   }
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
