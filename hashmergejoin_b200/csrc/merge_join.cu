@@ -24,7 +24,10 @@
 namespace {
 
 constexpr int JOIN_THREADS = 256;
-constexpr int JOIN_TILE = 4096;  // merged elements per tile
+#ifndef HMJ_JOIN_TILE
+#define HMJ_JOIN_TILE 4096
+#endif
+constexpr int JOIN_TILE = HMJ_JOIN_TILE;  // merged elements per tile
 constexpr int JOIN_VT = JOIN_TILE / JOIN_THREADS;  // merged elements per thread in the tile merge
 // hashes are stored padded (one extra slot per 8) so that threads walking their own chunk of the
 // merged order (stride ~8 per array) hit different banks
@@ -451,24 +454,37 @@ join_tile_kernel(const JoinArgs A) {
     const uint64_t t = block_reduce_u64(my_pairs, sh->tmp);
     if (tid == 0) {
       A.tile_counts[tile] = t;
-      if (MODE == JOIN_FUSED) {
-        // decoupled look-back over the tiles before this one
+      sh->p_off[0] = t;
+      if (MODE == JOIN_FUSED && tile != 0) jd_store(A.tile_desc + tile, JD_PARTIAL | t);
+    }
+    if (MODE == JOIN_FUSED) {
+      __syncthreads();
+      if (tid < 32) {
+        // decoupled look-back, one warp: 32 predecessor descriptors per round trip
+        const uint64_t mine = sh->p_off[0];
         uint64_t excl = 0;
-        if (tile != 0) {
-          jd_store(A.tile_desc + tile, JD_PARTIAL | t);
-          int64_t prev = (int64_t)tile - 1;
-          while (true) {
-            const uint64_t v = jd_load(A.tile_desc + prev);
-            if ((v >> 62) == 0) continue;
-            excl += v & JD_VALUE;
-            if ((v >> 62) == 2) break;
-            --prev;
+        int64_t first_idx = (int64_t)tile - 1;
+        while (first_idx >= 0) {
+          const int64_t idx = first_idx - tid;
+          uint64_t v = JD_INCLUSIVE;  // before tile 0: an inclusive prefix of zero
+          if (idx >= 0) {
+            v = jd_load(A.tile_desc + idx);
+            while ((v >> 62) == 0) v = jd_load(A.tile_desc + idx);
           }
+          const uint32_t incl = __ballot_sync(0xffffffffu, (v >> 62) == 2);
+          const int stop = incl ? (__ffs(incl) - 1) : 31;
+          uint64_t c = (tid <= stop) ? (v & JD_VALUE) : 0;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+          excl += c;
+          if (incl) break;
+          first_idx -= 32;
         }
-        jd_store(A.tile_desc + tile, JD_INCLUSIVE | (excl + t));
-        if (tile == A.tiles - 1) A.agg[2] = excl + t;
-        sh->base = excl;
-        sh->p_off[0] = t;
+        if (tid == 0) {
+          jd_store(A.tile_desc + tile, JD_INCLUSIVE | (excl + mine));
+          if (tile == A.tiles - 1) A.agg[2] = excl + mine;
+          sh->base = excl;
+        }
       }
     }
     if (MODE == JOIN_FUSED) {
