@@ -33,7 +33,7 @@ constexpr int JOIN_VT = JOIN_TILE / JOIN_THREADS;  // merged elements per thread
 // merged order (stride ~8 per array) hit different banks
 __host__ __device__ constexpr uint32_t jpad(uint32_t i) { return i + (i >> 3); }
 constexpr size_t JOIN_HASH_SLOTS = JOIN_TILE + JOIN_TILE / 8 + 2;
-constexpr size_t JOIN_SMEM_BASE = JOIN_HASH_SLOTS * 8 + (size_t)JOIN_TILE * 4 + (size_t)JOIN_TILE * 2 + 8192;
+constexpr size_t JOIN_SMEM_BASE = JOIN_HASH_SLOTS * 8 + (size_t)JOIN_TILE * 4 + 8192;
 constexpr size_t JOIN_SMEM_STR = JOIN_SMEM_BASE + (size_t)JOIN_TILE * 4;  // + verified counts
 
 enum JoinMode { JOIN_COUNT = 0, JOIN_WRITE = 1, JOIN_AGG = 2, JOIN_FUSED = 3 };
@@ -191,8 +191,9 @@ constexpr int JOIN_BIG = 64;
 struct JoinShared {  // lives behind the tile arrays in dynamic shared memory
   uint64_t tmp[JOIN_THREADS / 32 + 2];
   uint64_t p_off[JOIN_THREADS];
-  uint32_t p_rrow[JOIN_THREADS], p_lb[JOIN_THREADS], p_n[JOIN_THREADS], p_res[JOIN_THREADS];
+  uint32_t p_rrow[JOIN_THREADS], p_lb[JOIN_THREADS], p_n[JOIN_THREADS];  // p_n: in candidates, out verified
   uint32_t q[JOIN_THREADS];
+  uint64_t wt[JOIN_TILE / 32];  // fused mode: match totals per (round, warp), then their scan
   uint32_t qn;
   uint32_t tile;
   uint64_t base;
@@ -216,7 +217,7 @@ __device__ void coop_count(const JoinArgs& A, JoinShared* sh) {
     for (uint32_t t = threadIdx.x; t < n; t += JOIN_THREADS)
       c += cand_ok<KIND>(A, rrow, A.sr[lb + t]) ? 1 : 0;
     const uint64_t tot = block_reduce_u64(c, sh->tmp);
-    if (threadIdx.x == 0) sh->p_res[o] = (uint32_t)tot;
+    if (threadIdx.x == 0) sh->p_n[o] = (uint32_t)tot;  // every thread has read p_n[o] (reduce syncs)
   }
   __syncthreads();
   if (threadIdx.x == 0) sh->qn = 0;
@@ -290,8 +291,9 @@ __global__ void __launch_bounds__(JOIN_THREADS)
 join_tile_kernel(const JoinArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s_h = reinterpret_cast<uint64_t*>(smem_raw);               // R hashes then S hashes, padded
-  uint32_t* s_id = reinterpret_cast<uint32_t*>(s_h + JOIN_HASH_SLOTS); // [T] row ids, same order
-  uint16_t* s_lb = reinterpret_cast<uint16_t*>(s_id + JOIN_TILE);      // [T] lower bound in the S span
+  // [T] per R element: lower bound in the S span; fused mode later reuses the slot for the
+  // element's output offset inside its (round, warp) group
+  uint32_t* s_lb = reinterpret_cast<uint32_t*>(s_h + JOIN_HASH_SLOTS);
   JoinShared* sh = reinterpret_cast<JoinShared*>(s_lb + JOIN_TILE);
   uint32_t* s_cnt = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(sh) + 8192);  // strings
   constexpr bool NEED_IDS = (KIND == HMJ_KEY_STRING) || (MODE != JOIN_COUNT);
@@ -311,16 +313,11 @@ join_tile_kernel(const JoinArgs A) {
   const uint32_t na = a1 - a0, nb = b1 - b0;
 
   // R hashes at padded slots [0,na), S hashes at padded slots of (na + i)
-  for (uint32_t i = tid; i < na; i += JOIN_THREADS) {
-    s_h[jpad(i)] = __ldcs(A.rh + a0 + i);
-    if (NEED_IDS) s_id[i] = __ldcs(A.rr + a0 + i);
-  }
-  for (uint32_t i = tid; i < nb; i += JOIN_THREADS) {
-    s_h[jpad(na + i)] = __ldcs(A.sh + b0 + i);
-    if (NEED_IDS) s_id[na + i] = __ldcs(A.sr + b0 + i);
-  }
+  // (row ids are not staged: they are read from global memory where pairs are emitted --
+  // consecutive threads read consecutive entries)
+  for (uint32_t i = tid; i < na; i += JOIN_THREADS) s_h[jpad(i)] = __ldcs(A.rh + a0 + i);
+  for (uint32_t i = tid; i < nb; i += JOIN_THREADS) s_h[jpad(na + i)] = __ldcs(A.sh + b0 + i);
   __syncthreads();
-  const uint32_t* s_ids = s_id + na;
   auto RH = [&](uint32_t i) -> uint64_t { return s_h[jpad(i)]; };
   auto SH = [&](uint32_t i) -> uint64_t { return s_h[jpad(na + i)]; };
 
@@ -342,7 +339,7 @@ join_tile_kernel(const JoinArgs A) {
       if (a + b >= nt) break;
       const bool take_r = (b >= nb) || (a < na && ra <= sb);
       if (take_r) {
-        s_lb[a] = (uint16_t)b;
+        s_lb[a] = b;
         ++a;
         if (a < na) ra = RH(a);
       } else {
@@ -375,7 +372,7 @@ join_tile_kernel(const JoinArgs A) {
       const uint64_t rv = (MODE == JOIN_AGG) ? (A.rvals ? A.rvals[rrow] : (uint64_t)rrow) : 0;
       for (uint32_t t = 0; t < ncand; ++t) {
         const uint32_t j = lb + t;
-        const uint32_t srow = (j >= b0 && j < b1) ? s_ids[j - b0] : A.sr[j];
+        const uint32_t srow = A.sr[j];
         if (KIND == HMJ_KEY_STRING) {
           const bool ok = (have_mask && t < 64) ? ((vmask >> t) & 1) : cand_ok<KIND>(A, rrow, srow);
           if (!ok) continue;
@@ -392,6 +389,7 @@ join_tile_kernel(const JoinArgs A) {
     if (__syncthreads_or(big)) coop_emit<KIND, MODE>(A, sh, do_write, &my_sum);
   };
 
+  bool wide = false, any_big = false;  // fused: an offset needs 64 bits / a run is walked by the CTA
   // ---- phase A: equal-hash run of every R element, verified match count
   for (uint32_t r = 0; r < rounds; ++r) {
     const uint32_t li = r * JOIN_THREADS + tid;
@@ -416,7 +414,7 @@ join_tile_kernel(const JoinArgs A) {
       lb = b0 + l;
       const uint32_t ub = (u == nb) ? gallop_upper(A.sh, b1, A.ns, h) : b0 + u;
       ncand = ub - lb;
-      if (NEED_IDS) rrow = s_id[li];
+      if (NEED_IDS) rrow = A.rr[a0 + li];
       if (KIND == HMJ_KEY_U64) {
         cnt = ncand;
       } else if (ncand > (uint32_t)JOIN_BIG) {
@@ -426,7 +424,7 @@ join_tile_kernel(const JoinArgs A) {
       } else {
         for (uint32_t t = 0; t < ncand; ++t) {
           const uint32_t j = lb + t;
-          const uint32_t srow = (j < b1) ? s_ids[j - b0] : A.sr[j];
+          const uint32_t srow = A.sr[j];
           if (cand_ok<KIND>(A, rrow, srow)) {
             vmask |= 1ull << t;
             ++cnt;
@@ -437,64 +435,122 @@ join_tile_kernel(const JoinArgs A) {
     if (KIND == HMJ_KEY_STRING) {
       if (__syncthreads_or(big)) {
         coop_count<KIND>(A, sh);
-        if (big) cnt = sh->p_res[tid];
+        if (big) cnt = sh->p_n[tid];
       }
     }
     my_pairs += cnt;
     if (MODE == JOIN_WRITE || MODE == JOIN_AGG) {
       emit_round(active, rrow, lb, ncand, cnt, vmask, true);
-    } else if (MODE == JOIN_FUSED && active) {
-      // this thread alone reads R hash li from here on: reuse its slot for (lb, ncand)
-      s_h[jpad(li)] = (uint64_t)lb | ((uint64_t)ncand << 32);
-      if (KIND == HMJ_KEY_STRING) s_cnt[li] = cnt;
+    } else if (MODE == JOIN_FUSED) {
+      // offsets: inclusive scan of the match counts inside the warp now, (round, warp) totals
+      // are scanned once per tile below -- no block-wide scan per round
+      uint64_t x = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if ((tid & 31) >= o) x += y;
+      }
+      const uint64_t wexcl = x - cnt;
+      if ((tid & 31) == 31) sh->wt[r * (JOIN_THREADS / 32) + (tid >> 5)] = x;
+      if (active) {
+        // this thread alone reads R hash li from here on: reuse its slot for (lb, ncand)
+        s_h[jpad(li)] = (uint64_t)lb | ((uint64_t)ncand << 32);
+        s_lb[li] = (uint32_t)wexcl;
+        if (KIND == HMJ_KEY_STRING) s_cnt[li] = cnt;
+        if (wexcl >> 32) wide = true;
+        if (ncand > (uint32_t)JOIN_BIG) any_big = true;
+      }
     }
   }
 
-  if (MODE == JOIN_COUNT || MODE == JOIN_FUSED) {
+  if (MODE == JOIN_COUNT) {
     const uint64_t t = block_reduce_u64(my_pairs, sh->tmp);
-    if (tid == 0) {
-      A.tile_counts[tile] = t;
-      sh->p_off[0] = t;
-      if (MODE == JOIN_FUSED && tile != 0) jd_store(A.tile_desc + tile, JD_PARTIAL | t);
-    }
-    if (MODE == JOIN_FUSED) {
-      __syncthreads();
-      if (tid < 32) {
-        // decoupled look-back, one warp: 32 predecessor descriptors per round trip
-        const uint64_t mine = sh->p_off[0];
-        uint64_t excl = 0;
-        int64_t first_idx = (int64_t)tile - 1;
-        while (first_idx >= 0) {
-          const int64_t idx = first_idx - tid;
-          uint64_t v = JD_INCLUSIVE;  // before tile 0: an inclusive prefix of zero
-          if (idx >= 0) {
-            v = jd_load(A.tile_desc + idx);
-            while ((v >> 62) == 0) v = jd_load(A.tile_desc + idx);
-          }
-          const uint32_t incl = __ballot_sync(0xffffffffu, (v >> 62) == 2);
-          const int stop = incl ? (__ffs(incl) - 1) : 31;
-          uint64_t c = (tid <= stop) ? (v & JD_VALUE) : 0;
+    if (tid == 0) A.tile_counts[tile] = t;
+  } else if (MODE == JOIN_FUSED) {
+    const int flags = __syncthreads_or((wide ? 1 : 0) | (any_big ? 2 : 0));
+    if (tid < 32) {
+      // exclusive scan of the (round, warp) totals, in element order
+      constexpr int PER_LANE = JOIN_TILE / 32 / 32;
+      static_assert(PER_LANE >= 1, "tile too small for the warp scan layout");
+      const uint32_t groups = rounds * (JOIN_THREADS / 32);
+      uint64_t v[PER_LANE], sum = 0;
 #pragma unroll
-          for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-          excl += c;
-          if (incl) break;
-          first_idx -= 32;
+      for (int i = 0; i < PER_LANE; ++i) {
+        const uint32_t g = tid * PER_LANE + i;
+        v[i] = g < groups ? sh->wt[g] : 0;
+        sum += v[i];
+      }
+      uint64_t x = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint64_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if (tid >= o) x += y;
+      }
+      const uint64_t mine = __shfl_sync(0xffffffffu, x, 31);  // matches of the whole tile
+      uint64_t run = x - sum;
+#pragma unroll
+      for (int i = 0; i < PER_LANE; ++i) {
+        const uint32_t g = tid * PER_LANE + i;
+        if (g < groups) sh->wt[g] = run;
+        run += v[i];
+      }
+      if (tid == 0) {
+        A.tile_counts[tile] = mine;
+        sh->p_off[0] = mine;
+        if (tile != 0) jd_store(A.tile_desc + tile, JD_PARTIAL | mine);
+      }
+      // decoupled look-back, one warp: 32 predecessor descriptors per round trip
+      uint64_t excl = 0;
+      int64_t first_idx = (int64_t)tile - 1;
+      while (first_idx >= 0) {
+        const int64_t idx = first_idx - tid;
+        uint64_t d = JD_INCLUSIVE;  // before tile 0: an inclusive prefix of zero
+        if (idx >= 0) {
+          d = jd_load(A.tile_desc + idx);
+          while ((d >> 62) == 0) d = jd_load(A.tile_desc + idx);
         }
-        if (tid == 0) {
-          jd_store(A.tile_desc + tile, JD_INCLUSIVE | (excl + mine));
-          if (tile == A.tiles - 1) A.agg[2] = excl + mine;
-          sh->base = excl;
-        }
+        const uint32_t incl = __ballot_sync(0xffffffffu, (d >> 62) == 2);
+        const int stop = incl ? (__ffs(incl) - 1) : 31;
+        uint64_t c = (tid <= stop) ? (d & JD_VALUE) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+        excl += c;
+        if (incl) break;
+        first_idx -= 32;
+      }
+      if (tid == 0) {
+        jd_store(A.tile_desc + tile, JD_INCLUSIVE | (excl + mine));
+        if (tile == A.tiles - 1) A.agg[2] = excl + mine;
+        sh->base = excl;
       }
     }
-    if (MODE == JOIN_FUSED) {
-      __syncthreads();
-      running = sh->base;
-      const uint64_t tile_total = sh->p_off[0];
-      do_write = running + tile_total <= A.cap;
-      __syncthreads();
-      if (tile_total != 0 && do_write) {
-        // ---- phase B: emit with the offsets now known
+    __syncthreads();
+    const uint64_t tile_base = sh->base;
+    const uint64_t tile_total = sh->p_off[0];
+    do_write = tile_base + tile_total <= A.cap;
+    if (tile_total != 0 && do_write) {
+      // ---- phase B: emit with the offsets now known
+      if (flags == 0) {
+        // common case: short runs only, 32-bit offsets inside a (round, warp) group
+        for (uint32_t r = 0; r < rounds; ++r) {
+          const uint32_t li = r * JOIN_THREADS + tid;
+          if (li >= na) break;
+          const uint64_t w = s_h[jpad(li)];
+          const uint32_t lb = (uint32_t)w, ncand = (uint32_t)(w >> 32);
+          if (ncand == 0) continue;
+          uint64_t off = tile_base + sh->wt[r * (JOIN_THREADS / 32) + (tid >> 5)] + s_lb[li];
+          const uint32_t rrow = A.rr[a0 + li];
+          for (uint32_t t = 0; t < ncand; ++t) {
+            const uint32_t srow = A.sr[lb + t];
+            if (KIND == HMJ_KEY_STRING && !cand_ok<KIND>(A, rrow, srow)) continue;
+            A.out_r[off] = rrow;
+            A.out_s[off] = srow;
+            ++off;
+          }
+        }
+      } else {
+        // long runs (walked by the whole CTA) or 64-bit offsets: block scan per round
+        running = tile_base;
         for (uint32_t r = 0; r < rounds; ++r) {
           const uint32_t li = r * JOIN_THREADS + tid;
           const bool active = li < na;
@@ -504,7 +560,7 @@ join_tile_kernel(const JoinArgs A) {
             lb = (uint32_t)w;
             ncand = (uint32_t)(w >> 32);
             cnt = (KIND == HMJ_KEY_STRING) ? s_cnt[li] : ncand;
-            rrow = s_id[li];
+            rrow = A.rr[a0 + li];
           }
           emit_round(active, rrow, lb, ncand, cnt, 0, false);
         }
