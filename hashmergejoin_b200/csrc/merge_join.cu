@@ -531,21 +531,39 @@ join_tile_kernel(const JoinArgs A) {
     if (tile_total != 0 && do_write) {
       // ---- phase B: emit with the offsets now known
       if (flags == 0) {
-        // common case: short runs only, 32-bit offsets inside a (round, warp) group
-        for (uint32_t r = 0; r < rounds; ++r) {
-          const uint32_t li = r * JOIN_THREADS + tid;
-          if (li >= na) break;
-          const uint64_t w = s_h[jpad(li)];
-          const uint32_t lb = (uint32_t)w, ncand = (uint32_t)(w >> 32);
-          if (ncand == 0) continue;
-          uint64_t off = tile_base + sh->wt[r * (JOIN_THREADS / 32) + (tid >> 5)] + s_lb[li];
-          const uint32_t rrow = A.rr[a0 + li];
-          for (uint32_t t = 0; t < ncand; ++t) {
-            const uint32_t srow = A.sr[lb + t];
-            if (KIND == HMJ_KEY_STRING && !cand_ok<KIND>(A, rrow, srow)) continue;
-            A.out_r[off] = rrow;
-            A.out_s[off] = srow;
-            ++off;
+        // common case: short runs only, 32-bit offsets inside a (round, warp) group.  Rounds
+        // are taken four at a time so that the row-id loads of a group are all in flight
+        // before the first store waits on one of them.
+        constexpr int G = 4;
+        for (uint32_t r0 = 0; r0 < rounds; r0 += G) {
+          uint32_t lb[G], nc[G], rrow[G], srow[G];
+          uint64_t off[G];
+#pragma unroll
+          for (int g = 0; g < G; ++g) {
+            const uint32_t r = r0 + g, li = r * JOIN_THREADS + tid;
+            nc[g] = 0;
+            if (r < rounds && li < na) {
+              const uint64_t w = s_h[jpad(li)];
+              lb[g] = (uint32_t)w;
+              nc[g] = (uint32_t)(w >> 32);
+              if (nc[g]) {
+                off[g] = tile_base + sh->wt[r * (JOIN_THREADS / 32) + (tid >> 5)] + s_lb[li];
+                rrow[g] = A.rr[a0 + li];
+                srow[g] = A.sr[lb[g]];
+              }
+            }
+          }
+#pragma unroll
+          for (int g = 0; g < G; ++g) {
+            if (nc[g] == 0) continue;
+            uint64_t o = off[g];
+            for (uint32_t t = 0; t < nc[g]; ++t) {
+              const uint32_t sr = t == 0 ? srow[g] : A.sr[lb[g] + t];
+              if (KIND == HMJ_KEY_STRING && !cand_ok<KIND>(A, rrow[g], sr)) continue;
+              A.out_r[o] = rrow[g];
+              A.out_s[o] = sr;
+              ++o;
+            }
           }
         }
       } else {
