@@ -1,0 +1,166 @@
+// hashjoin.h (facade) -- HashMergeJoin / HashMergeJoin2 of dryman/HashMergeJoin hashjoin.h:33-363
+// with the same constructor arguments and the same input-iterator protocol
+// (begin()/end()/clear(), *it -> std::tuple<Key*, RValue*, SValue*>&), backed by the B200
+// hash -> radix sort -> merge join (libhmj.so).
+//
+// Semantics: the TRUE equi-join -- every (r, s) with equal keys, duplicate runs expanded as the
+// full cross product, key equality verified on every hash match.  The reference iterator emits
+// a subset on N:M runs and stops when either cursor reaches its last element (DESIGN.md,
+// "reference defects"); on unique keys both agree.
+// Lifetime: like the reference, dereferenced pointers alias storage owned by the operator and
+// die with clear() / the operator.
+#ifndef HASH_JOIN_H
+#define HASH_JOIN_H 1
+
+#include <string>
+#include <tuple>
+#include <utility>
+#include <vector>
+
+#include "radix_hash.h"
+
+typedef std::vector<std::pair<std::string, uint64_t>> KeyValVec;
+typedef std::vector<std::tuple<std::size_t, std::string, uint64_t>> HashKeyValVec;
+
+namespace hmj {
+namespace detail {
+
+// GPU join of two flattened key columns -> (build_row, probe_row) pairs.
+// For kHostHash keys only hash equality is decided on the device; the caller filters by key.
+template <typename Key, typename Hash>
+void join_columns(const KeyColumns& r, const KeyColumns& s, std::vector<uint32_t>* out_r,
+                  std::vector<uint32_t>* out_s) {
+  hmj_ctx* ctx = Context::get();
+  uint64_t m = 0;
+  const bool str = key_path<Key, Hash>::value == kString;
+  if (str)
+    Context::check(hmj_join_strings_host(ctx, r.offsets.data(), r.chars.data(), r.n, s.offsets.data(),
+                                         s.chars.data(), s.n, nullptr, nullptr, 0, &m),
+                   "hmj_join_strings_host");
+  else
+    Context::check(hmj_join_u64_host(ctx, r.u64.data(), r.n, s.u64.data(), s.n, nullptr, nullptr, 0, &m),
+                   "hmj_join_u64_host");
+  out_r->resize(m);
+  out_s->resize(m);
+  if (m) Context::check(hmj_join_result_to_host(ctx, out_r->data(), out_s->data(), m),
+                        "hmj_join_result_to_host");
+}
+
+// The iterator both operators hand out: walks the materialised pair list.
+template <typename Key, typename RValue, typename SValue>
+class JoinCursor : public std::iterator<std::input_iterator_tag, std::tuple<Key*, RValue*, SValue*>> {
+ public:
+  typedef std::tuple<Key*, RValue*, SValue*> value_type;
+  JoinCursor(const std::vector<value_type>* rows, std::size_t pos) : rows_(rows), pos_(pos) { load(); }
+  JoinCursor& operator++() { ++pos_; load(); return *this; }
+  JoinCursor operator++(int) { JoinCursor t(*this); ++*this; return t; }
+  bool operator==(const JoinCursor& o) const { return pos_ == o.pos_; }
+  bool operator!=(const JoinCursor& o) const { return pos_ != o.pos_; }
+  value_type& operator*() { return cur_; }
+  value_type* operator->() { return &cur_; }
+
+ private:
+  void load() { if (rows_ && pos_ < rows_->size()) cur_ = (*rows_)[pos_]; }
+  const std::vector<value_type>* rows_;
+  std::size_t pos_;
+  value_type cur_;
+};
+
+}  // namespace detail
+}  // namespace hmj
+
+template <typename RIter, typename SIter>
+class HashMergeJoin {
+  static_assert(std::is_same<typename RIter::value_type::first_type,
+                             typename SIter::value_type::first_type>::value,
+                "RIter and SIter key type must be the same");
+  typedef typename RIter::value_type::first_type Key;
+  typedef typename RIter::value_type::second_type RValue;
+  typedef typename SIter::value_type::second_type SValue;
+  typedef std::hash<Key> Hash;
+
+ public:
+  typedef hmj::detail::JoinCursor<Key, RValue, SValue> iterator;
+
+  HashMergeJoin() = default;
+  HashMergeJoin(RIter r_begin, RIter r_end, SIter s_begin, SIter s_end,
+                unsigned int /*num_threads*/ = 1) {
+    // the operator owns copies of both relations (reference: _r_sorted/_s_sorted, :62-63)
+    _r.assign(r_begin, r_end);
+    _s.assign(s_begin, s_end);
+    const hmj::detail::KeyColumns rc =
+        hmj::detail::flatten<Key, Hash>(_r.begin(), _r.end(), radix_hash::detail::first_of());
+    const hmj::detail::KeyColumns sc =
+        hmj::detail::flatten<Key, Hash>(_s.begin(), _s.end(), radix_hash::detail::first_of());
+    std::vector<uint32_t> pr, ps;
+    hmj::detail::join_columns<Key, Hash>(rc, sc, &pr, &ps);
+    const bool verify = hmj::detail::key_path<Key, Hash>::value == hmj::detail::kHostHash;
+    _rows.reserve(pr.size());
+    for (std::size_t i = 0; i < pr.size(); ++i) {
+      if (verify && !(_r[pr[i]].first == _s[ps[i]].first)) continue;
+      _rows.push_back(std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second));
+    }
+  }
+
+  iterator begin() { return iterator(&_rows, 0); }
+  iterator end() { return iterator(&_rows, _rows.size()); }
+  void clear() {
+    _rows.clear();
+    _r.clear();
+    _s.clear();
+  }
+
+ protected:
+  std::vector<std::pair<Key, RValue>> _r;
+  std::vector<std::pair<Key, SValue>> _s;
+  std::vector<std::tuple<Key*, RValue*, SValue*>> _rows;
+};
+
+// Pre-hashed tuples (hash, key, value) owned by the caller; both ranges are sorted in place on
+// the hash column (reference :224-236 calls radix_inplace_par) and then merge-joined.
+template <typename RIter, typename SIter>
+class HashMergeJoin2 {
+  static_assert(std::is_same<typename std::tuple_element<1, typename RIter::value_type>::type,
+                             typename std::tuple_element<1, typename SIter::value_type>::type>::value,
+                "RIter and SIter key type must be the same");
+  typedef typename std::tuple_element<1, typename RIter::value_type>::type Key;
+  typedef typename std::tuple_element<2, typename RIter::value_type>::type RValue;
+  typedef typename std::tuple_element<2, typename SIter::value_type>::type SValue;
+
+ public:
+  typedef hmj::detail::JoinCursor<Key, RValue, SValue> iterator;
+
+  HashMergeJoin2() = default;
+  HashMergeJoin2(RIter r_begin, RIter r_end, SIter s_begin, SIter s_end, unsigned int num_threads = 1)
+      : _r_begin(r_begin), _r_end(r_end), _s_begin(s_begin), _s_end(s_end) {
+    const std::size_t nr = std::distance(r_begin, r_end), ns = std::distance(s_begin, s_end);
+    radix_hash::radix_inplace_par(_r_begin, nr, (int)num_threads);
+    radix_hash::radix_inplace_par(_s_begin, ns, (int)num_threads);
+    // join on the caller's hash column; keys are compared on the host for every hash match
+    hmj::detail::KeyColumns rc, sc;
+    rc.n = nr;
+    sc.n = ns;
+    for (RIter it = r_begin; it != r_end; ++it) rc.u64.push_back((uint64_t)std::get<0>(*it));
+    for (SIter it = s_begin; it != s_end; ++it) sc.u64.push_back((uint64_t)std::get<0>(*it));
+    std::vector<uint32_t> pr, ps;
+    struct caller_hash {};  // any non-std::hash type selects the shipped-hash (u64) path
+    hmj::detail::join_columns<Key, caller_hash>(rc, sc, &pr, &ps);
+    for (std::size_t i = 0; i < pr.size(); ++i) {
+      auto& r = _r_begin[pr[i]];
+      auto& s = _s_begin[ps[i]];
+      if (!(std::get<1>(r) == std::get<1>(s))) continue;
+      _rows.push_back(std::make_tuple(&std::get<1>(r), &std::get<2>(r), &std::get<2>(s)));
+    }
+  }
+
+  iterator begin() { return iterator(&_rows, 0); }
+  iterator end() { return iterator(&_rows, _rows.size()); }
+  void clear() { _rows.clear(); }
+
+ protected:
+  RIter _r_begin, _r_end;
+  SIter _s_begin, _s_end;
+  std::vector<std::tuple<Key*, RValue*, SValue*>> _rows;
+};
+
+#endif  // HASH_JOIN_H
