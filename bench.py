@@ -98,10 +98,13 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
-    """dram bytes per onesweep launch from the committed ncu capture, if one exists."""
+def ncu_traffic(alg_bytes):
+    """dram__bytes_read.sum + dram__bytes_write.sum per onesweep launch from the committed
+    `ncu --set full` capture (profiles/roofline_traffic.json), scaled from the captured launch's
+    pair count to this run's by the ratio of algorithmic bytes; None when no capture exists."""
     try:
-        return json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))["onesweep_pass_bytes_per_launch"]
+        t = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+        return t["dram_bytes_per_launch"] * alg_bytes / t["algorithmic_bytes_per_launch"]
     except Exception:
         return None
 
@@ -250,22 +253,28 @@ def run_gpu(args):
     ms_per_step = elapsed_ms / args.steps
     value = 2 * rows_total / (ms_per_step * 1e-3)
 
-    # ---- roofline of the dominant kernel (onesweep pass), timed per launch during the steps
+    # ---- roofline of the dominant kernel (onesweep scatter pass), timed per launch with CUDA
+    # events on the launching stream during the timed steps (hmj_set_profiling)
     peak, peak_src = peaks()
-    n_local = rows if world == 1 else None
     pass_launches = max(tm["pass_launches"], 1)
     avg_pass_ms = tm["pass_ms_sum"] / pass_launches
+    passes_per_sort = pass_launches / (2.0 * args.steps)
     if world == 1:
-        # per launch: 12 B read + 12 B written per pair; the first pass of each sort reads 8
-        # (row ids are generated, not loaded): (7*24 + 20)/8 = 23.5 B per pair on average
-        alg_bytes = rows * 23.5
+        # per launch: 12 B read + 12 B written per pair; the first pass of each sort reads only
+        # the 8-byte keys (row ids are generated, not loaded)
+        alg_bytes = rows * (24.0 - 4.0 / passes_per_sort)
     else:
-        alg_bytes = joiner.avg_pass_pairs() * 24.0
+        # pairs arrive from the exchange with explicit row ids: every pass moves 24 B per pair;
+        # the partition pass (K8) over the local block reads 8 and writes 12
+        nr_loc, ns_loc = joiner.local_rows
+        sort_launches = pass_launches - 2 * args.steps
+        alg_bytes = ((nr_loc + ns_loc) / 2.0 * 24.0 * sort_launches + rows * 20.0 * 2 * args.steps) / pass_launches
     achieved = alg_bytes / (avg_pass_ms * 1e-3) / 1e9 if avg_pass_ms > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": "onesweep_pass_kernel", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_ms": avg_pass_ms,
-                "launches_timed": tm["pass_launches"],
+                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(alg_bytes),
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
+                "avg_launch_ms": avg_pass_ms, "launches_timed": tm["pass_launches"],
+                "passes_per_sort": passes_per_sort,
                 "share_of_step": tm["pass_ms_sum"] / elapsed_ms if elapsed_ms else None}
 
     # ---- e2e: host buffers through the C ABI (H2D + join + D2H of the pairs), N=1 only here
@@ -294,6 +303,44 @@ def run_gpu(args):
         e2e = {"value": 2 * rows / dt, "unit": UNIT, "h2d_bytes_per_step": 2 * rows * 8,
                "d2h_bytes_per_step": 2 * rows * 4, "ms_per_step": dt * 1e3, "steps": e2e_steps,
                "api": "hmj_join_u64_host (pinned host buffers)"}
+    elif world > 1 and not args.no_e2e:
+        # every rank: pinned host block of both relations -> H2D -> partition / all-to-all /
+        # sort / merge join -> D2H of this rank's pairs.  Wall clock between barriers, max over ranks.
+        h_r = torch.empty(rows, dtype=torch.int64).pin_memory()
+        h_s = torch.empty(rows, dtype=torch.int64).pin_memory()
+        h_r.copy_(rkeys)
+        h_s.copy_(skeys)
+        cap = int(rows * 1.25) + 1024
+        o_r = torch.empty(cap, dtype=torch.int32).pin_memory()
+        o_s = torch.empty(cap, dtype=torch.int32).pin_memory()
+
+        def e2e_step():
+            rkeys.copy_(h_r, non_blocking=True)
+            skeys.copy_(h_s, non_blocking=True)
+            m, (out_r, out_s, _, _) = joiner.join_u64(rkeys, skeys, want_pairs=True)
+            assert m <= cap
+            o_r[:m].copy_(out_r, non_blocking=True)
+            o_s[:m].copy_(out_s, non_blocking=True)
+            torch.cuda.synchronize()
+            return m
+
+        e2e_steps = max(1, min(args.steps, 3))
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            m = e2e_step()
+        barrier()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        t = torch.tensor([dt], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        t = torch.tensor([m], dtype=torch.int64, device=device)
+        dist.all_reduce(t)
+        assert int(t.item()) == rows_total
+        e2e = {"value": 2 * rows_total / dt, "unit": UNIT, "h2d_bytes_per_step": 2 * rows_total * 8,
+               "d2h_bytes_per_step": 2 * rows_total * 4, "ms_per_step": dt * 1e3, "steps": e2e_steps,
+               "api": "DistJoin.join_u64 (per-rank pinned host blocks; bytes are whole-job totals)"}
 
     if rank == 0:
         cpu = None
@@ -308,10 +355,15 @@ def run_gpu(args):
             "config": {"workload": wl_desc, "rows_per_side": rows_total, "rows_per_side_per_gpu": rows,
                        "key": "u64 (splitmix64 of a row permutation; same key set both sides)",
                        "l2": "inputs (2 x %.1f GB) and every intermediate exceed the 126 MB L2; no flush needed" % (rows * 8 / 1e9),
-                       "sort_passes_per_join": tm["sort_passes"], "parallelism": "hash-range partition x%d" % world},
+                       "sort_passes_per_join": tm["sort_passes"], "bucket_finishes_per_join": tm["sort_finishes"],
+                       "sort_fallbacks": tm["sort_fallbacks"],
+                       "parallelism": "hash-range partition x%d" % world},
             "stage_ms_last_step": {k: tm[k] for k in ("hash_ms", "sort_ms", "join_ms", "total_ms")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
         }
+        if world > 1:
+            line["nvlink"] = {"exchange_bytes_sent_rank0_per_step": joiner.exchange_bytes,
+                              "note": "12 B per pair leaving the rank, both relations"}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

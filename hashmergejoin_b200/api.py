@@ -129,16 +129,24 @@ class Context:
         self._ck(self.lib.hmj_merge_join_count(self.h, C.byref(r), C.byref(s), C.byref(m)))
         return m.value
 
-    def merge_join(self, R, S):
-        m = self.merge_join_count(R, S)
-        out_r = self._empty(m, self._torch.int32)
-        out_s = self._empty(m, self._torch.int32)
-        m2 = C.c_uint64()
+    def merge_join(self, R, S, cap=None):
+        """Fused single-pass join.  First try with room for max(|R|,|S|) pairs (enough for any
+        join with unique keys on one side); an overflowing join reports the exact count and is
+        re-run into a buffer of that size."""
+        nr, ns = R.hash.numel(), S.hash.numel()
+        cap = max(nr, ns, 1) if cap is None else cap
         r, s = R.as_struct(), S.as_struct()
-        self._ck(self.lib.hmj_merge_join_write(self.h, C.byref(r), C.byref(s), _dptr(out_r),
-                                               _dptr(out_s), m, C.byref(m2)))
-        assert m2.value == m
-        return out_r, out_s
+        while True:
+            out_r = self._empty(cap, self._torch.int32)
+            out_s = self._empty(cap, self._torch.int32)
+            m = C.c_uint64()
+            rc = self.lib.hmj_merge_join_write(self.h, C.byref(r), C.byref(s), _dptr(out_r),
+                                               _dptr(out_s), cap, C.byref(m))
+            if rc == _lib.HMJ_ECAPACITY and m.value > cap:
+                cap = m.value
+                continue
+            self._ck(rc)
+            return out_r[:m.value], out_s[:m.value]
 
     def merge_join_aggregate(self, R, S, rvals=None, svals=None):
         m, sm = C.c_uint64(), C.c_uint64()
