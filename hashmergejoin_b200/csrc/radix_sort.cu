@@ -349,14 +349,19 @@ constexpr int FIN_HALO = 512;
 constexpr int FIN_MAX_BUCKET = 512;
 constexpr int FIN_SPAN = FIN_TILE + FIN_HALO;
 
+// IN PLACE: only the key column is read (8 B per pair); an element moves only when its rank
+// inside the bucket differs from its position, and then its row id moves with it.  With the
+// planner's prefix (buckets of ~1 element on average) almost nothing moves.
+//
 // fast path data: one 32-bit word per element = (31 key bits just below the prefix) << 1 | head
 // flag (first element of its bucket).  Ranking walks compare these words; two bucket-mates that
 // agree on all 31 bits but differ in the full key (possible only when shift > 31) send the
 // tile to the slow path, which repeats the walks on the full 64-bit keys.
 __global__ void __launch_bounds__(FIN_THREADS)
-bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, uint32_t n,
+bucket_finish_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, uint32_t n,
                      int shift, uint32_t* __restrict__ flag) {
+  constexpr int ITERS = (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS;
+  constexpr uint32_t NONE = 0xffffffffu;
   __shared__ uint64_t s_k[FIN_SPAN + 1];   // [0] = element before the tile
   __shared__ uint32_t s_sub[FIN_SPAN + 1]; // [avail] = sentinel head
   __shared__ uint16_t s_src[FIN_SPAN + 1]; // source index of the element ranked at a position
@@ -366,10 +371,10 @@ bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
   const int tid = threadIdx.x;
   const bool has_pred = tile_start != 0;
   if (tid == 0) {
-    s_k[0] = has_pred ? keys_in[tile_start - 1] : 0;
+    s_k[0] = has_pred ? keys[tile_start - 1] : 0;
     s_tie = 0;
   }
-  for (uint32_t i = tid; i < avail; i += FIN_THREADS) s_k[1 + i] = keys_in[tile_start + i];
+  for (uint32_t i = tid; i < avail; i += FIN_THREADS) s_k[1 + i] = keys[tile_start + i];
   __syncthreads();
   const int sub_shift = shift > 31 ? shift - 31 : 0;
   const uint64_t sub_mask = shift >= 31 ? 0x7fffffffull : ((1ull << shift) - 1);
@@ -388,13 +393,14 @@ bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
   const bool straddle = has_pred && (shift >= 64 || ((s_k[1] ^ s_k[0]) >> shift) == 0);
   const bool more_after = tile_start + avail < n;
 
-  uint32_t my_pos[(FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS];
+  uint32_t my_pos[ITERS];  // new position (tile-relative) of an element that has to move
 #pragma unroll
-  for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
+  for (int it = 0; it < ITERS; ++it) {
     const uint32_t i = it * FIN_THREADS + tid;
-    my_pos[it] = 0xffffffffu;
+    my_pos[it] = NONE;
     if (i >= avail) continue;
     const uint32_t me = s_sub[i];
+    if ((me & 1u) && (s_sub[i + 1] & 1u)) continue;  // bucket of one element
     const uint32_t me_le = me | 1u, me_lt = me & ~1u;
     uint32_t rank = 0, o = me, j = i;
     while (!(o & 1u)) {
@@ -416,17 +422,17 @@ bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
       continue;
     }
     my_pos[it] = start + rank;
-    s_src[start + rank] = (uint16_t)i;
+    if (shift > 31) s_src[start + rank] = (uint16_t)i;
   }
-  __syncthreads();
   // tie check: my successor in ranked order, if a bucket-mate with the same 31 bits, must
   // also have the same full key
   if (shift > 31) {
+    __syncthreads();
 #pragma unroll
-    for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
+    for (int it = 0; it < ITERS; ++it) {
       const uint32_t i = it * FIN_THREADS + tid;
       const uint32_t p = my_pos[it];
-      if (p == 0xffffffffu) continue;
+      if (p == NONE) continue;
       const uint32_t nxt = s_src[p + 1];
       if (nxt == 0xffff) continue;
       if (((s_sub[nxt] ^ s_sub[i]) >> 1) == 0 &&
@@ -435,45 +441,59 @@ bucket_finish_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
         s_tie = 1;
     }
     __syncthreads();
-  }
-  if (s_tie == 0) {
+    if (s_tie != 0) {
+      // slow path: same ranking on the full keys
+      const uint64_t low_mask = shift >= 64 ? ~0ull : ((1ull << shift) - 1);
 #pragma unroll
-    for (int it = 0; it < (FIN_SPAN + FIN_THREADS - 1) / FIN_THREADS; ++it) {
-      const uint32_t i = it * FIN_THREADS + tid;
-      const uint32_t p = my_pos[it];
-      if (p == 0xffffffffu) continue;
-      keys_out[tile_start + p] = s_k[1 + i];
-      vals_out[tile_start + p] = vals_in ? vals_in[tile_start + i] : tile_start + i;
+      for (int it = 0; it < ITERS; ++it) {
+        const uint32_t i = it * FIN_THREADS + tid;
+        my_pos[it] = NONE;
+        if (i >= avail) continue;
+        const uint64_t key = s_k[1 + i];
+        const uint64_t lo = key & ~low_mask, hi = key | low_mask;  // key range of my bucket
+        uint32_t rank = 0;
+        int j = (int)i - 1;
+        while (j >= 0) {
+          const uint64_t o = s_k[1 + j];
+          if (o < lo) break;
+          rank += (o <= key) ? 1u : 0u;
+          --j;
+        }
+        const uint32_t start = (uint32_t)(j + 1);
+        if (start >= (uint32_t)FIN_TILE) continue;
+        if (j < 0 && has_pred && s_k[0] >= lo) continue;
+        uint32_t e = i + 1;
+        while (e < avail) {
+          const uint64_t o = s_k[1 + e];
+          if (o > hi) break;
+          rank += (o < key) ? 1u : 0u;
+          ++e;
+        }
+        if ((e == avail && more_after) || e - start > (uint32_t)FIN_MAX_BUCKET) continue;  // flagged above
+        my_pos[it] = start + rank;
+      }
     }
-    return;
   }
-  // slow path: same ranking on the full keys
-  const uint64_t low_mask = shift >= 64 ? ~0ull : ((1ull << shift) - 1);
-  for (uint32_t i = tid; i < avail; i += FIN_THREADS) {
-    const uint64_t key = s_k[1 + i];
-    const uint64_t lo = key & ~low_mask, hi = key | low_mask;  // key range of my bucket
-    uint32_t rank = 0;
-    int j = (int)i - 1;
-    while (j >= 0) {
-      const uint64_t o = s_k[1 + j];
-      if (o < lo) break;
-      rank += (o <= key) ? 1u : 0u;
-      --j;
+  // ---- move phase: row ids of every moving element are read before anything is written
+  // (buckets are owned by exactly one CTA, so nobody else writes these positions)
+  uint32_t my_val[ITERS];
+  bool moving = false;
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) {
+    const uint32_t i = it * FIN_THREADS + tid;
+    if (my_pos[it] == i) my_pos[it] = NONE;  // already in place
+    if (my_pos[it] != NONE) {
+      my_val[it] = vals[tile_start + i];
+      moving = true;
     }
-    const uint32_t start = (uint32_t)(j + 1);
-    if (start >= (uint32_t)FIN_TILE) continue;
-    if (j < 0 && has_pred && s_k[0] >= lo) continue;
-    uint32_t e = i + 1;
-    while (e < avail) {
-      const uint64_t o = s_k[1 + e];
-      if (o > hi) break;
-      rank += (o < key) ? 1u : 0u;
-      ++e;
-    }
-    if ((e == avail && more_after) || e - start > (uint32_t)FIN_MAX_BUCKET) continue;  // flagged above
-    const uint32_t dst = tile_start + start + rank;
-    keys_out[dst] = key;
-    vals_out[dst] = vals_in ? vals_in[tile_start + i] : tile_start + i;
+  }
+  if (!__syncthreads_or(moving)) return;
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) {
+    const uint32_t i = it * FIN_THREADS + tid;
+    if (my_pos[it] == NONE) continue;
+    keys[tile_start + my_pos[it]] = s_k[1 + i];
+    vals[tile_start + my_pos[it]] = my_val[it];
   }
 }
 
@@ -569,8 +589,8 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   struct Buf { uint64_t* k; uint32_t* v; };
   Buf bufs[2] = {{keys_out, vals_out}, {nullptr, nullptr}};
   const bool aliased = (keys_in == keys_out) || (vals_in != nullptr && vals_in == vals_out);
-  int steps = nd + (finish_shift >= 0 ? 1 : 0);
-  if (steps == 0) {  // nothing to do: copy through
+  int steps = nd;  // the bucket finish works in place
+  if (steps == 0 && finish_shift < 0) {  // nothing to do: copy through
     if (keys_in != keys_out)
       HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
     if (vals_in == nullptr) {
@@ -640,54 +660,46 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   // be overwritten by the step that reads it, so it goes to the workspace first
   int first_dst = (steps - 1) & 1;
   if (aliased && first_dst == 0) first_dst = 1;
-  int where = first_dst ^ 1;
-  HMJ_TRY(run_passes(keys_in, vals_in, digits, nd, first_dst, &where));
-  ctx->tm.sort_passes += (uint32_t)nd;
+  int where = 0;
+  if (nd > 0) {
+    HMJ_TRY(run_passes(keys_in, vals_in, digits, nd, first_dst, &where));
+    ctx->tm.sort_passes += (uint32_t)nd;
+  } else {
+    // no scatter pass (tiny input, or the prefix digits are all trivial): the pairs go to the
+    // output columns as they are and the finish orders them there
+    if (keys_in != keys_out)
+      HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
+    if (vals_in == nullptr) {
+      iota_kernel<<<(int)min(hmj_div_up(n, 256), (size_t)ctx->num_sms * 8), 256, 0, st>>>(vals_out, n32);
+      HMJ_LAUNCHED(ctx);
+    } else if (vals_in != vals_out) {
+      HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, vals_in, n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    where = 0;
+  }
 
   if (finish_shift >= 0) {
-    const uint64_t* fk = nd ? bufs[where].k : keys_in;
-    const uint32_t* fv = nd ? bufs[where].v : vals_in;  // null (nd == 0 only) = iota
-    const int fdst = first_dst ^ (nd & 1);
     bucket_finish_kernel<<<(unsigned)hmj_div_up(n, FIN_TILE), FIN_THREADS, 0, st>>>(
-        fk, fv, bufs[fdst].k, bufs[fdst].v, n32, finish_shift, d_flag);
+        bufs[where].k, bufs[where].v, n32, finish_shift, d_flag);
     HMJ_LAUNCHED(ctx);
     ctx->tm.sort_finishes += 1;
     uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
     HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     HMJ_CUDA(ctx, cudaStreamSynchronize(st));
-    if (h[0] == 0) {
-      where = fdst;
-    } else {
-      // A bucket was too large.  The finish input (the caller's input, or the prefix-sorted
-      // pairs: a stable permutation of it) is intact, so it is re-sorted from there with
-      // stable scatter passes over every non-trivial digit; the result is the same.
+    if (h[0] != 0) {
+      // A bucket was too large.  What the finish left behind is still a permutation of the
+      // input that keeps equal keys in input order, so stable scatter passes over every
+      // non-trivial digit, started from there, give the same result as a sort of the input.
       ctx->tm.sort_fallbacks += 1;
       int all[NUM_PASSES], na = 0;
       for (int d = 0; d < NUM_PASSES; ++d)
         if (!trivial[d]) all[na++] = d;
-      if (na == 0) {
-        // every key is equal: the input order is the sorted order
-        HMJ_ARG(ctx, nd == 0);
-        steps = 0;
-        if (keys_in != keys_out)
-          HMJ_CUDA(ctx, cudaMemcpyAsync(keys_out, keys_in, n * 8, cudaMemcpyDeviceToDevice, st));
-        if (vals_in == nullptr) {
-          iota_kernel<<<(int)min(hmj_div_up(n, 256), (size_t)ctx->num_sms * 8), 256, 0, st>>>(vals_out, n32);
-          HMJ_LAUNCHED(ctx);
-        } else if (vals_in != vals_out) {
-          HMJ_CUDA(ctx, cudaMemcpyAsync(vals_out, vals_in, n * 4, cudaMemcpyDeviceToDevice, st));
-        }
-        return HMJ_OK;
+      if (na > 0) {
+        const int src = where;
+        HMJ_TRY(run_passes(bufs[src].k, bufs[src].v, all, na, src ^ 1, &where));
+        ctx->tm.sort_passes += (uint32_t)na;
       }
-      int fd2;
-      if (nd == 0) {
-        fd2 = (na - 1) & 1;
-        if (aliased && fd2 == 0) fd2 = 1;
-      } else {
-        fd2 = where ^ 1;
-      }
-      HMJ_TRY(run_passes(fk, fv, all, na, fd2, &where));
-      ctx->tm.sort_passes += (uint32_t)na;
+      // na == 0: every key is equal, the order is already right
     }
   }
   if (where != 0) {
