@@ -35,6 +35,7 @@ enum hmj_ws_slot {
   WS_IN_3,
   WS_TABLE,         // hash-join baseline table
   WS_SCALARS,       // small device scalars (counters, sums)
+  WS_SEG_WINDOWS,   // window table of the segment sort
   WS_NUM_SLOTS
 };
 
@@ -120,5 +121,9 @@ static inline size_t hmj_div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 // (implemented in hash.cu / radix_sort.cu / merge_join.cu / hash_table.cu / partition.cu)
 int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* d_keys_in, const uint32_t* d_vals_in, size_t n,
                   uint64_t* d_keys_out, uint32_t* d_vals_out);
+// segment_sort.cu
+int hmj_segment_sort_cap();
+int hmj_launch_segment_sort(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, uint32_t n, int q,
+                            int per_prefix, uint32_t stride, uint32_t* d_flag);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
                          uint64_t* h_num_pairs);

@@ -501,7 +501,7 @@ struct DigitStats { uint32_t nz, maxbin; };
 
 int hybrid_from_env() {
   const char* e = getenv("HMJ_SORT_HYBRID");
-  return e ? atoi(e) : 1;
+  return e ? atoi(e) : 2;
 }
 
 }  // namespace
@@ -541,7 +541,9 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   // finish is enough.  Small sorts skip the read-back and run every pass.
   DigitStats stats[NUM_PASSES];
   for (int p = 0; p < NUM_PASSES; ++p) stats[p] = {RADIX, 0};
-  const bool planned = n >= (size_t(1) << 15);
+  const int hyb = hybrid_from_env();
+  const uint32_t seg_cap = (uint32_t)hmj_segment_sort_cap();
+  const bool planned = hyb == 2 ? n > seg_cap : n >= (size_t(1) << 15);
   if (planned) {
     uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
     HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_stats, 2 * NUM_PASSES * sizeof(uint32_t),
@@ -553,9 +555,48 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   for (int p = 0; p < NUM_PASSES; ++p) trivial[p] = planned && stats[p].maxbin == n32;
 
   int digits[NUM_PASSES], nd = 0;  // scatter passes of the first attempt, ascending
-  int finish_shift = -1;           // >= 0: bucket finish on key >> finish_shift
-  bool hybrid = hybrid_from_env() != 0 && (planned || n <= (size_t)FIN_MAX_BUCKET);
-  if (hybrid) {
+  int finish_shift = -1;           // >= 0: finish on the buckets of key >> finish_shift
+  int finish_kind = 0;             // 1 = bucket finish (in place, small buckets), 2 = segment sort
+  bool seg_per_prefix = false;     // segment sort: one window per prefix value
+  const uint32_t seg_stride = seg_cap - 1024;  // mode B: segments up to 1024 pairs fit
+  if (hyb == 2 && n <= seg_cap) {
+    finish_kind = 2;  // the whole array is one window
+    finish_shift = 64;
+  } else if (hyb == 2 && planned) {
+    // Scatter on the top digits until the prefix cuts the array into segments the segment sort
+    // takes in one window: either one window per prefix value (dense digits, mean + 8 sigma
+    // within the window capacity) or several small segments per window.
+    double max_avg_a = seg_cap;
+    while (max_avg_a + 8.0 * sqrt(max_avg_a) > (double)seg_cap) max_avg_a -= 16.0;
+    const double max_avg_b = 640.0;
+    double eff = 0;
+    int q = 0;
+    bool skewed = false, dense = true;
+    while (q < NUM_PASSES) {
+      const double avg = (double)n / exp2(eff);
+      if (dense && q > 0 && q <= 2 && avg <= max_avg_a && avg > max_avg_b) {
+        seg_per_prefix = true;
+        break;
+      }
+      if (avg <= max_avg_b) break;
+      const int d = NUM_PASSES - 1 - q;
+      if (!trivial[d]) {
+        const double mean = (double)n / stats[d].nz;
+        if ((double)stats[d].maxbin > mean + 8.0 * sqrt(mean) + 64.0) skewed = true;
+        eff += log2((double)stats[d].nz);
+        if (stats[d].nz != RADIX) dense = false;
+      } else {
+        dense = false;
+      }
+      ++q;
+    }
+    if (!skewed && q < NUM_PASSES) {
+      finish_kind = 2;
+      finish_shift = 64 - RADIX_BITS * q;
+      for (int d = NUM_PASSES - q; d < NUM_PASSES; ++d)
+        if (!trivial[d]) digits[nd++] = d;
+    }
+  } else if (hyb == 1 && (planned || n <= (size_t)FIN_MAX_BUCKET)) {
     // include top digits until the prefix separates the keys into buckets of <= ~16..32
     const double need = n <= (size_t)FIN_MAX_BUCKET / 2 ? 0.0 : floor(log2((double)n)) - 3.0;
     double eff = 0;
@@ -571,20 +612,19 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
       }
       ++q;
     }
-    if (skewed || eff < need || nontrivial >= NUM_PASSES - 1) {
-      hybrid = false;
-    } else {
+    if (!(skewed || eff < need || nontrivial >= NUM_PASSES - 1)) {
       finish_shift = RADIX_BITS * (NUM_PASSES - q);
-      if (finish_shift == 0) finish_shift = -1;  // the prefix is the whole key: plain LSD sort
+      if (finish_shift != 0) finish_kind = 1;  // else the prefix is the whole key: plain LSD
+      else finish_shift = -1;
       for (int d = NUM_PASSES - q; d < NUM_PASSES; ++d)
         if (!trivial[d]) digits[nd++] = d;
     }
   }
-  if (!hybrid) {
-    nd = 0;
+  if (finish_kind == 0 && finish_shift < 0 && nd == 0) {
     for (int d = 0; d < NUM_PASSES; ++d)
       if (!trivial[d]) digits[nd++] = d;
   }
+  if (finish_kind == 0) finish_shift = -1;
 
   struct Buf { uint64_t* k; uint32_t* v; };
   Buf bufs[2] = {{keys_out, vals_out}, {nullptr, nullptr}};
@@ -679,9 +719,14 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   }
 
   if (finish_shift >= 0) {
-    bucket_finish_kernel<<<(unsigned)hmj_div_up(n, FIN_TILE), FIN_THREADS, 0, st>>>(
-        bufs[where].k, bufs[where].v, n32, finish_shift, d_flag);
-    HMJ_LAUNCHED(ctx);
+    if (finish_kind == 2) {
+      HMJ_TRY(hmj_launch_segment_sort(ctx, bufs[where].k, bufs[where].v, n32, 64 - finish_shift,
+                                      seg_per_prefix ? 1 : 0, seg_stride, d_flag));
+    } else {
+      bucket_finish_kernel<<<(unsigned)hmj_div_up(n, FIN_TILE), FIN_THREADS, 0, st>>>(
+          bufs[where].k, bufs[where].v, n32, finish_shift, d_flag);
+      HMJ_LAUNCHED(ctx);
+    }
     ctx->tm.sort_finishes += 1;
     uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
     HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
