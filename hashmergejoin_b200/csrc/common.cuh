@@ -124,6 +124,6 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* d_keys_in, const uint32_t* d_val
 // segment_sort.cu
 int hmj_segment_sort_cap();
 int hmj_launch_segment_sort(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, uint32_t n, int q,
-                            int per_prefix, uint32_t stride, uint32_t* d_flag);
+                            int group_shift, uint32_t stride, uint32_t* d_flag);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
                          uint64_t* h_num_pairs);

@@ -557,7 +557,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   int digits[NUM_PASSES], nd = 0;  // scatter passes of the first attempt, ascending
   int finish_shift = -1;           // >= 0: finish on the buckets of key >> finish_shift
   int finish_kind = 0;             // 1 = bucket finish (in place, small buckets), 2 = segment sort
-  bool seg_per_prefix = false;     // segment sort: one window per prefix value
+  int seg_group_shift = -1;        // segment sort: >= 0 = windows of 2^shift prefix values
   const uint32_t seg_stride = seg_cap - 1024;  // mode B: segments up to 1024 pairs fit
   if (hyb == 2 && n <= seg_cap) {
     finish_kind = 2;  // the whole array is one window
@@ -574,9 +574,12 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
     bool skewed = false, dense = true;
     while (q < NUM_PASSES) {
       const double avg = (double)n / exp2(eff);
-      if (dense && q > 0 && q <= 2 && avg <= max_avg_a && avg > max_avg_b) {
-        seg_per_prefix = true;
-        break;
+      if (dense && q > 0 && avg <= max_avg_a && avg > max_avg_b) {
+        // windows of g prefix values, g the largest power of two with g * avg <= max_avg_a
+        seg_group_shift = (int)floor(log2(max_avg_a / avg));
+        seg_group_shift = min(seg_group_shift, RADIX_BITS * q);
+        if (RADIX_BITS * q - seg_group_shift <= 20) break;
+        seg_group_shift = -1;
       }
       if (avg <= max_avg_b) break;
       const int d = NUM_PASSES - 1 - q;
@@ -721,7 +724,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   if (finish_shift >= 0) {
     if (finish_kind == 2) {
       HMJ_TRY(hmj_launch_segment_sort(ctx, bufs[where].k, bufs[where].v, n32, 64 - finish_shift,
-                                      seg_per_prefix ? 1 : 0, seg_stride, d_flag));
+                                      seg_group_shift, seg_stride, d_flag));
     } else {
       bucket_finish_kernel<<<(unsigned)hmj_div_up(n, FIN_TILE), FIN_THREADS, 0, st>>>(
           bufs[where].k, bufs[where].v, n32, finish_shift, d_flag);

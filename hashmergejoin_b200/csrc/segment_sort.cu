@@ -31,7 +31,7 @@ template <int THREADS, int ITEMS>
 struct SegCfg {
   static constexpr int CAP = THREADS * ITEMS;
   static constexpr size_t SMEM_BYTES =
-      (size_t)CAP * 8 + (size_t)CAP * 4 + (size_t)(SEG_BINS + 1) * 4 + 32 * 4 + 16;
+      (size_t)(CAP + 4) * 8 + (size_t)CAP * 4 + (size_t)(SEG_BINS + 1) * 4 + 32 * 4 + 16;
 };
 
 template <int THREADS, int ITEMS, int MIN_BLOCKS>
@@ -41,10 +41,12 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
   using Cfg = SegCfg<THREADS, ITEMS>;
   constexpr int CAP = Cfg::CAP;
   constexpr int PER = (SEG_BINS + THREADS - 1) / THREADS;  // bins scanned per thread
+  constexpr int IDX_BITS = 13;
+  static_assert(CAP <= (1 << IDX_BITS), "window positions must fit IDX_BITS");
 
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
-  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + CAP);
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + CAP + 4);
   uint16_t* s_idx = reinterpret_cast<uint16_t*>(s_vals);  // dead before s_vals is written
   uint32_t* s_bin = s_vals + CAP;                         // [SEG_BINS + 1] counts, then starts
   uint32_t* s_warp = s_bin + SEG_BINS + 1;                // [32]
@@ -123,8 +125,11 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
       if (tid == 0) atomicOr(flag, 1u);
       return;
     }
-    uint32_t pre = x - sum;
-    for (int w = 0; w < warp; ++w) pre += s_warp[w];
+    // totals of the warps before mine, summed with shuffles (THREADS / 32 <= 32 warps)
+    uint32_t wt = (lane < warp && lane < THREADS / 32) ? s_warp[lane] : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    uint32_t pre = wt + x - sum;
 #pragma unroll
     for (int j = 0; j < PER; ++j) {
       const int b = tid * PER + j;
@@ -135,36 +140,65 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
   }
   __syncthreads();
 
-  // bin order in shared memory
+  if (s <= 64 - IDX_BITS) {
+    // fast path: one word per pair = (key bits below the digit) << IDX_BITS | window position.
+    // It is unique and orders bin-mates exactly like (key, position), so ranking is one
+    // comparison per bin-mate.
+    const uint64_t rem_mask = (1ull << s) - 1;
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    const uint32_t i = tid + k * THREADS;
-    if (i < len) {
-      const uint32_t d = (uint32_t)((key[k] - base) >> s);
-      const uint32_t p = s_bin[d] + slot[k];
-      s_keys[p] = key[k];
-      s_idx[p] = (uint16_t)i;
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t i = tid + k * THREADS;
+      if (i < len) {
+        const uint64_t rel = key[k] - base;
+        const uint32_t d = (uint32_t)(rel >> s);
+        s_keys[s_bin[d] + slot[k]] = ((rel & rem_mask) << IDX_BITS) | i;
+      }
     }
-  }
-  __syncthreads();
-
-  // rank inside the bin on (key, window position)
+    __syncthreads();
 #pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    const uint32_t i = tid + k * THREADS;
-    if (i < len) {
-      const uint32_t d = (uint32_t)((key[k] - base) >> s);
-      const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
-      uint32_t p = b0 + slot[k];
-      if (b1 - b0 > 1) {
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t i = tid + k * THREADS;
+      if (i < len) {
+        const uint64_t rel = key[k] - base;
+        const uint32_t d = (uint32_t)(rel >> s);
+        const uint64_t me = ((rel & rem_mask) << IDX_BITS) | i;
+        const uint32_t b0 = s_bin[d], c = s_bin[d + 1] - b0;
+        uint32_t r = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+          const uint64_t o = s_keys[b0 + j];  // may read past the bin: masked by j < c
+          r += (j < c && o < me) ? 1u : 0u;
+        }
+        for (uint32_t j = 4; j < c; ++j) r += (s_keys[b0 + j] < me) ? 1u : 0u;
+        slot[k] = (uint16_t)(b0 + r);
+      }
+    }
+  } else {
+    // generic path (a window that spans nearly the whole key range): full key, then position
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t i = tid + k * THREADS;
+      if (i < len) {
+        const uint32_t d = (uint32_t)((key[k] - base) >> s);
+        const uint32_t p = s_bin[d] + slot[k];
+        s_keys[p] = key[k];
+        s_idx[p] = (uint16_t)i;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t i = tid + k * THREADS;
+      if (i < len) {
+        const uint32_t d = (uint32_t)((key[k] - base) >> s);
+        const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
         uint32_t r = 0;
         for (uint32_t j = b0; j < b1; ++j) {
           const uint64_t o = s_keys[j];
           r += (o < key[k] || (o == key[k] && s_idx[j] < (uint16_t)i)) ? 1u : 0u;
         }
-        p = b0 + r;
+        slot[k] = (uint16_t)(b0 + r);
       }
-      slot[k] = (uint16_t)p;
     }
   }
   __syncthreads();
@@ -188,12 +222,13 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
 }
 
 // win[0..nwin]: window w is [win[w], win[w+1]).
-//   mode A (stride == 0): window w = the segment of prefix value w, nwin = 2^q.
+//   mode A (stride == 0): window w = the segments of prefix values [w << gshift, (w+1) << gshift),
+//   nwin = 2^(q - gshift).
 //   mode B (stride  > 0): window w starts at the first segment boundary at or after w*stride;
 //   the search is bounded by `reach` pairs (a longer segment overflows the window anyway).
 __global__ void segment_windows_kernel(const uint64_t* __restrict__ keys, uint32_t n, int q,
-                                       uint32_t stride, uint32_t reach, uint32_t nwin,
-                                       uint32_t* __restrict__ win) {
+                                       uint32_t stride, int gshift, uint32_t reach,
+                                       uint32_t nwin, uint32_t* __restrict__ win) {
   const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
   if (w > nwin) return;
   if (w == nwin) {
@@ -210,7 +245,7 @@ __global__ void segment_windows_kernel(const uint64_t* __restrict__ keys, uint32
   if (stride == 0) {
     lo = 0;
     hi = n;
-    target = w;
+    target = (uint64_t)w << gshift;
   } else {
     const uint64_t pos64 = (uint64_t)w * stride;
     if (pos64 >= n) {
@@ -241,28 +276,31 @@ using SegDefault = SegCfg<512, 9>;
 
 int hmj_segment_sort_cap() { return SegDefault::CAP; }
 
-// Sorts (keys, vals), already ordered on key >> (64 - q), in place.  per_prefix != 0 selects
-// mode A (needs q <= 20 and every prefix segment <= CAP), else mode B with windows of
-// `stride` pairs.  *d_flag is OR-ed with 1 when a window or bin was too large.
+// Sorts (keys, vals), already ordered on key >> (64 - q), in place.  group_shift >= 0 selects
+// mode A (windows of 2^group_shift prefix values; needs q - group_shift <= 20 and every window
+// <= CAP), group_shift < 0 mode B with windows of `stride` pairs.  *d_flag is OR-ed with 1 when
+// a window or bin was too large.
 int hmj_launch_segment_sort(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, uint32_t n, int q,
-                            int per_prefix, uint32_t stride, uint32_t* d_flag) {
-  HMJ_ARG(ctx, q >= 0 && q <= 56 && (!per_prefix || q <= 20));
+                            int group_shift, uint32_t stride, uint32_t* d_flag) {
+  HMJ_ARG(ctx, q >= 0 && q <= 56 && (group_shift < 0 || (group_shift <= q && q - group_shift <= 20)));
   cudaStream_t st = ctx->stream;
   uint32_t nwin;
   if (q == 0) {
     nwin = 1;
     stride = n;
-  } else if (per_prefix) {
-    nwin = 1u << q;
+    group_shift = 0;
+  } else if (group_shift >= 0) {
+    nwin = 1u << (q - group_shift);
     stride = 0;
   } else {
     HMJ_ARG(ctx, stride > 0);
     nwin = (uint32_t)hmj_div_up(n, stride);
+    group_shift = 0;
   }
   uint32_t* d_win = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_SEG_WINDOWS, (size_t)nwin + 1, &d_win));
   segment_windows_kernel<<<(nwin + 1 + 255) / 256, 256, 0, st>>>(
-      keys, n, q, stride, (uint32_t)SegDefault::CAP + 2, nwin, d_win);
+      keys, n, q, stride, group_shift, (uint32_t)SegDefault::CAP + 2, nwin, d_win);
   HMJ_LAUNCHED(ctx);
   auto kern = segment_sort_kernel<512, 9, 2>;
   HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
