@@ -50,3 +50,12 @@ $(BUILD)/facade_test: tests/cpp/facade_test.cc $(wildcard $(FACADE)/*.h) include
 
 clean:
 	rm -rf $(BUILD) $(LIB) oracle/libhmj_oracle.so oracle/_ref
+
+# ---- instrumented build (per-tile timeline of the scatter pass; scripts/trace_pass.py) ----
+TRACE_OBJS := $(patsubst $(CSRC)/%.cu,$(BUILD)/trace/%.o,$(CU_SRCS))
+$(BUILD)/trace/%.o: $(CSRC)/%.cu $(CU_HDRS)
+	@mkdir -p $(BUILD)/trace
+	$(NVCC) $(NVFLAGS) -DHMJ_TRACE -c $< -o $@
+trace: $(BUILD)/trace/libhmj.so
+$(BUILD)/trace/libhmj.so: $(TRACE_OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $^ -lcudart_static -lpthread -ldl -lrt

@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhmj.so")
+# HMJ_LIB_PATH: an instrumented build of the same library (scripts/trace_pass.py), never a fallback
+LIB_PATH = os.environ.get("HMJ_LIB_PATH") or os.path.join(_HERE, "libhmj.so")
 
 HMJ_OK = 0
 HMJ_EARG, HMJ_ECUDA, HMJ_ENOMEM, HMJ_ENODEVICE, HMJ_ECAPACITY = -1, -2, -3, -4, -5
@@ -42,6 +43,8 @@ class Timings(C.Structure):
         ("total_ms", C.c_float), ("sort_passes", C.c_uint32),
         ("pass_ms_sum", C.c_float), ("pass_launches", C.c_uint32),
         ("sort_finishes", C.c_uint32), ("sort_fallbacks", C.c_uint32),
+        ("sort_uniform", C.c_uint32), ("kernel_launches", C.c_uint32 * 8),
+        ("kernel_ms", C.c_float * 8), ("kernel_bytes", C.c_double * 8),
     ]
 
 

@@ -250,7 +250,10 @@ class Context:
     def timings(self):
         t = Timings()
         self._ck(self.lib.hmj_get_timings(self.h, C.byref(t)))
-        return {k: getattr(t, k) for k, _ in Timings._fields_}
+        out = {k: getattr(t, k) for k, _ in Timings._fields_}
+        for k in ("kernel_launches", "kernel_ms", "kernel_bytes"):
+            out[k] = list(out[k])
+        return out
 
 
 def optimal_partition(n):

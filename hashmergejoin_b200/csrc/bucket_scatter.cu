@@ -1,0 +1,280 @@
+// bucket_scatter.cu -- K3u: the "uniform hash" sort of (u64 hash, u32 row-id) pairs.
+//
+// The reference partitions on the top hash bits first (radix_hash.h:351-423) and then refines
+// every partition independently (radix_hash.h:122-292): an MSD radix sort, which needs no stable
+// passes because a partition is never mixed with another again.  On the GPU that removes the
+// decoupled look-back chain of the stable LSD pass (profiles/r1c: a tile of the onesweep pass
+// spends 6 of its 14 us walking back through ~40 earlier tiles) and the warp ranking:
+//   level 1/2  bucket_scatter_kernel: a CTA counts its tile's digits with shared-memory atomics,
+//              reserves room in every destination bucket with ONE global atomicAdd per bucket
+//              (order of arrival, not of tile id) and writes its runs there.  Buckets live in
+//              fixed-capacity regions (mean + 8 sigma of a uniform hash), so no histogram pass
+//              is needed before the data moves.
+//   finish     segment_sort_kernel (segment_sort.cu) sorts every final bucket (~2^11..2^12
+//              pairs) in shared memory on the remaining key bits, breaks ties on the row id, and
+//              writes the dense, fully ordered output.  (key, row id) ascending is exactly what
+//              the stable sort produces from iota row ids, so the result is canonical.
+// A bucket that overflows its region (skewed or heavily duplicated hashes) raises *flag; the
+// caller then runs the histogram-planned stable sort on the untouched input.
+// Algorithmic bytes per pair: level 1 reads 8 (+4 with row ids) and writes 12; level 2 reads 12
+// and writes 12; finish reads 12 and writes 12.
+#include "common.cuh"
+
+namespace {
+
+constexpr int US_THREADS = 256;
+constexpr int US_ITEMS = 16;
+constexpr int US_TILE = US_THREADS * US_ITEMS;
+constexpr int US_MAX_BINS = 256;
+constexpr int US_CURSOR_STRIDE = 1;  // words between cursors (see uniform_plan)
+constexpr size_t US_SMEM = (size_t)US_TILE * 12 + 3 * US_MAX_BINS * 4 + 64;
+
+// Input: `regions_in` regions of `in_stride` slots, region r holding in_counts[r] pairs (or one
+// region of n_single pairs when in_counts == nullptr).  CTA b takes tile b % tiles_per_region of
+// region b / tiles_per_region.  Output bucket of a pair = (r << bits) | digit, stored in the
+// region [bucket * out_cap, (bucket + 1) * out_cap) at the slot reserved through cursors[bucket].
+__global__ void __launch_bounds__(US_THREADS, 3)
+bucket_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                      const uint32_t* __restrict__ in_counts, uint32_t in_stride,
+                      uint32_t n_single, uint32_t tiles_per_region, uint32_t iota_base,
+                      uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift,
+                      int bits, uint32_t out_cap, uint32_t* __restrict__ cursors,
+                      uint32_t* __restrict__ flag) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + US_TILE);
+  uint32_t* s_cnt = s_vals + US_TILE;       // [bins] tile counts
+  uint32_t* s_off = s_cnt + US_MAX_BINS;    // [bins] start of the digit inside the tile
+  uint32_t* s_gbase = s_off + US_MAX_BINS;  // [bins] global slot of the digit's run minus s_off
+  uint32_t* s_scan = s_gbase + US_MAX_BINS; // [8]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t r = blockIdx.x / tiles_per_region, j = blockIdx.x % tiles_per_region;
+  // (a region that overflowed holds in_stride pairs at most; the flag is up and the result void)
+  const uint32_t count = in_counts ? min(in_counts[r * US_CURSOR_STRIDE], in_stride) : n_single;
+  const uint64_t tile_first = (uint64_t)j * US_TILE;
+  if (tile_first >= count) return;
+  // the attempt is already void once any bucket has overflowed
+  if (__syncthreads_or(tid == 0 && *reinterpret_cast<volatile uint32_t*>(flag) != 0)) return;
+  const uint32_t valid = (uint32_t)min((uint64_t)US_TILE, count - tile_first);
+  const uint32_t in_base = r * in_stride + (uint32_t)tile_first;
+  const int bins = 1 << bits;
+  const uint32_t mask = (uint32_t)bins - 1;
+
+  if (tid < bins) s_cnt[tid] = 0;
+  uint64_t key[US_ITEMS];
+#pragma unroll
+  for (int k = 0; k < US_ITEMS; ++k) {
+    const uint32_t i = tid + k * US_THREADS;
+    key[k] = i < valid ? __ldcs(keys_in + in_base + i) : 0;
+  }
+  __syncthreads();
+
+  uint16_t slot[US_ITEMS];
+#pragma unroll
+  for (int k = 0; k < US_ITEMS; ++k) {
+    const uint32_t i = tid + k * US_THREADS;
+    if (i < valid) slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+  }
+  __syncthreads();
+
+  // one reservation per destination bucket; the scan over the tile counts runs while the global
+  // atomics are in flight
+  uint32_t c = 0, old = 0, bucket = 0;
+  if (tid < bins) {
+    c = s_cnt[tid];
+    bucket = (r << bits) | (uint32_t)tid;
+    if (c) old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
+  }
+  {
+    uint32_t x = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_scan[warp] = x;
+    __syncthreads();
+    uint32_t wt = lane < warp ? s_scan[lane] : 0;  // 8 warps
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    wt = __shfl_sync(0xffffffffu, wt, 0);
+    if (tid < bins) s_off[tid] = wt + x - c;
+  }
+  __syncthreads();
+
+  // tile-sorted order in shared memory, so that a bucket's run leaves as consecutive stores
+  uint16_t pos[US_ITEMS];
+#pragma unroll
+  for (int k = 0; k < US_ITEMS; ++k) {
+    const uint32_t i = tid + k * US_THREADS;
+    if (i < valid) {
+      const uint32_t p = s_off[(uint32_t)(key[k] >> shift) & mask] + slot[k];
+      pos[k] = (uint16_t)p;
+      s_keys[p] = key[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < US_ITEMS; ++k) {
+    const uint32_t i = tid + k * US_THREADS;
+    if (i < valid) s_vals[pos[k]] = vals_in ? __ldcs(vals_in + in_base + i) : in_base + i + iota_base;
+  }
+  bool over = false;
+  if (tid < bins) {
+    over = c != 0 && (old > out_cap || c > out_cap - old);
+    s_gbase[tid] = bucket * out_cap + old - s_off[tid];
+  }
+  if (__syncthreads_or(over)) {
+    if (tid == 0) atomicOr(flag, 1u);
+    return;
+  }
+#pragma unroll 4
+  for (uint32_t i = tid; i < valid; i += US_THREADS) {
+    const uint64_t kk = s_keys[i];
+    const uint32_t dst = s_gbase[(uint32_t)(kk >> shift) & mask] + i;
+    keys_out[dst] = kk;
+    vals_out[dst] = s_vals[i];
+  }
+}
+
+// exclusive scan of the final bucket counts -> dense output offsets (one CTA; <= 2^18 buckets)
+__global__ void __launch_bounds__(1024)
+bucket_offsets_kernel(const uint32_t* __restrict__ counts, uint32_t buckets,
+                      uint32_t* __restrict__ offsets) {
+  __shared__ uint32_t s_warp[32];
+  __shared__ uint32_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < buckets; base += 1024) {
+    const uint32_t i = base + tid;
+    const uint32_t c = i < buckets ? counts[(size_t)i * US_CURSOR_STRIDE] : 0;
+    uint32_t x = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) s_warp[warp] = x;
+    __syncthreads();
+    uint32_t wt = lane < warp ? s_warp[lane] : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    const uint32_t carry = s_carry;
+    if (i < buckets) offsets[i] = carry + wt + x - c;
+    __syncthreads();
+    if (tid == 1023) s_carry = carry + wt + x;
+    __syncthreads();
+  }
+  if (tid == 0) offsets[buckets] = s_carry;
+}
+
+}  // namespace
+
+namespace {
+
+int uniform_from_env() {
+  const char* e = getenv("HMJ_SORT_UNIFORM");
+  return e ? atoi(e) : 1;
+}
+
+struct UniformPlan {
+  int levels = 0;       // 0 = not eligible
+  int bits[2] = {0, 0};
+  int qb = 0;           // total prefix bits = bits[0] + bits[1]
+  uint32_t cap1 = 0;    // slots per level-1 region (two levels only)
+  uint32_t cap_seg = 0; // slots per final bucket
+};
+
+// Final buckets of (2048, 4096] pairs on average; one or two scatter levels of <= 8 bits.
+UniformPlan uniform_plan(size_t n) {
+  UniformPlan p;
+  const uint32_t cap_seg = (uint32_t)hmj_segment_sort_cap();
+  if (n <= cap_seg) return p;
+  int qb = 0;
+  while (((n + ((size_t)1 << qb) - 1) >> qb) > 4096) ++qb;
+  if (qb > 16) return p;
+  p.qb = qb;
+  p.cap_seg = cap_seg;
+  if (qb <= 8) {
+    p.levels = 1;
+    p.bits[0] = qb;
+  } else {
+    p.levels = 2;
+    p.bits[0] = (qb + 1) / 2;
+    p.bits[1] = qb - p.bits[0];
+    const double avg1 = (double)n / (double)(1u << p.bits[0]);
+    const double c = avg1 + 8.0 * sqrt(avg1) + 64.0;
+    p.cap1 = ((uint32_t)c + 255u) & ~255u;
+  }
+  return p;
+}
+
+}  // namespace
+
+// Sorts (keys_in[i], iota_base + i) by (key, row id) with the uniform-hash path.  *ok = 0 when
+// the input is not eligible or a bucket overflowed (nothing usable was written; the input is
+// untouched).  keys_in must not alias keys_out.
+int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                         uint64_t* keys_out, uint32_t* vals_out, int* ok) {
+  *ok = 0;
+  if (uniform_from_env() == 0 || keys_in == keys_out) return HMJ_OK;
+  const UniformPlan p = uniform_plan(n);
+  if (p.levels == 0) return HMJ_OK;
+  cudaStream_t st = ctx->stream;
+  const uint32_t n32 = (uint32_t)n;
+  const uint32_t regions1 = 1u << p.bits[0], buckets = 1u << p.qb;
+
+  // scratch words: [flag][level-1 cursors][final cursors][final offsets + 1]
+  uint32_t* d_words = nullptr;
+  const size_t words = 8 + (size_t)regions1 + buckets + buckets + 1;
+  HMJ_TRY(hmj_ws(ctx, WS_US_CURSORS, words, &d_words));
+  uint32_t* d_flag = d_words;
+  uint32_t* d_cur1 = d_words + 8;
+  uint32_t* d_cur2 = p.levels == 2 ? d_cur1 + regions1 : d_cur1;
+  uint32_t* d_off = d_cur1 + regions1 + buckets;
+  HMJ_CUDA(ctx, cudaMemsetAsync(d_words, 0, (8 + (size_t)regions1 + buckets) * sizeof(uint32_t), st));
+
+  uint64_t *d_k1 = nullptr, *d_k2 = nullptr;
+  uint32_t *d_v1 = nullptr, *d_v2 = nullptr;
+  const size_t slots2 = (size_t)buckets * p.cap_seg;
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_B, slots2, &d_k2));
+  HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_B, slots2, &d_v2));
+  if (p.levels == 2) {
+    const size_t slots1 = (size_t)regions1 * p.cap1;
+    HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, slots1, &d_k1));
+    HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, slots1, &d_v1));
+  }
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
+  cudaEvent_t ev;
+  // level 1: the raw key column -> 2^bits[0] regions
+  const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
+  bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
+      keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
+      p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0], p.levels == 2 ? p.cap1 : p.cap_seg,
+      d_cur1, d_flag);
+  HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev);
+  if (p.levels == 2) {
+    const uint32_t tpr = (uint32_t)hmj_div_up(p.cap1, US_TILE);
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
+    bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
+        d_k1, d_v1, d_cur1, p.cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg, d_cur2,
+        d_flag);
+    HMJ_LAUNCHED(ctx);
+    hmj_prof_end(ctx, ev);
+  }
+  bucket_offsets_kernel<<<1, 1024, 0, st>>>(d_cur2, buckets, d_off);
+  HMJ_LAUNCHED(ctx);
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_FINISH, (double)n * 24.0, &ev));
+  HMJ_TRY(hmj_launch_bucket_finish(ctx, d_k2, d_v2, d_cur2, d_off, buckets, p.cap_seg, p.qb,
+                                   keys_out, vals_out, d_flag));
+  hmj_prof_end(ctx, ev);
+  uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+  *ok = h[0] == 0;
+  return HMJ_OK;
+}

@@ -36,6 +36,9 @@ enum hmj_ws_slot {
   WS_TABLE,         // hash-join baseline table
   WS_SCALARS,       // small device scalars (counters, sums)
   WS_SEG_WINDOWS,   // window table of the segment sort
+  WS_US_CURSORS,    // uniform sort: flag, bucket cursors, dense offsets
+  WS_HASH_TMP0,     // unsorted hash columns (strings), so that the sort never runs in place
+  WS_HASH_TMP1,
   WS_NUM_SLOTS
 };
 
@@ -61,6 +64,8 @@ struct hmj_ctx {
   // optional per-launch timing of the dominant kernel (onesweep pass), see hmj_set_profiling
   bool prof_on = false;
   std::vector<cudaEvent_t> prof_events;  // pairs: [2i] before, [2i+1] after launch i
+  std::vector<int> prof_kind;            // kernel class of pair i (hmj_kernel_class)
+  std::vector<double> prof_bytes;        // algorithmic bytes of launch i
   size_t prof_used = 0;
   // last whole-operator result
   uint64_t last_pairs = 0;
@@ -115,6 +120,32 @@ static inline int hmj_ws(hmj_ctx* ctx, int slot, size_t count, T** out) {
   return rc;
 }
 
+// Per-launch timing of the hot kernels while hmj_set_profiling is on: bracket a launch with
+//   cudaEvent_t after; HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_x, bytes, &after)); <launch>; hmj_prof_end(ctx, after);
+// `bytes` = algorithmic bytes the launch moves.
+static inline int hmj_prof_begin(hmj_ctx* ctx, int kind, double bytes, cudaEvent_t* after) {
+  *after = nullptr;
+  if (!ctx->prof_on) return HMJ_OK;
+  if (ctx->prof_used + 2 > ctx->prof_events.size()) {
+    cudaEvent_t a, b;
+    HMJ_CUDA(ctx, cudaEventCreate(&a));
+    HMJ_CUDA(ctx, cudaEventCreate(&b));
+    ctx->prof_events.push_back(a);
+    ctx->prof_events.push_back(b);
+    ctx->prof_kind.push_back(0);
+    ctx->prof_bytes.push_back(0);
+  }
+  ctx->prof_kind[ctx->prof_used / 2] = kind;
+  ctx->prof_bytes[ctx->prof_used / 2] = bytes;
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->prof_events[ctx->prof_used], ctx->stream));
+  *after = ctx->prof_events[ctx->prof_used + 1];
+  ctx->prof_used += 2;
+  return HMJ_OK;
+}
+static inline void hmj_prof_end(hmj_ctx* ctx, cudaEvent_t after) {
+  if (after) cudaEventRecord(after, ctx->stream);
+}
+
 static inline size_t hmj_div_up(size_t a, size_t b) { return (a + b - 1) / b; }
 
 // ---- stage entry points shared between translation units -----------------------------
@@ -125,5 +156,11 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* d_keys_in, const uint32_t* d_val
 int hmj_segment_sort_cap();
 int hmj_launch_segment_sort(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, uint32_t n, int q,
                             int group_shift, uint32_t stride, uint32_t* d_flag);
+int hmj_launch_bucket_finish(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, const uint32_t* counts,
+                             const uint32_t* offsets, uint32_t buckets, uint32_t in_cap, int q,
+                             uint64_t* out_keys, uint32_t* out_vals, uint32_t* d_flag);
+// bucket_scatter.cu
+int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                         uint64_t* keys_out, uint32_t* vals_out, int* ok);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
                          uint64_t* h_num_pairs);

@@ -31,6 +31,7 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   ctx->tm.sort_passes = 0;
   ctx->tm.sort_finishes = 0;
   ctx->tm.sort_fallbacks = 0;
+  ctx->tm.sort_uniform = 0;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));  // identity hash: no kernel
   hmj_relation R = {}, S = {};
@@ -56,6 +57,7 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   ctx->tm.sort_passes = 0;
   ctx->tm.sort_finishes = 0;
   ctx->tm.sort_fallbacks = 0;
+  ctx->tm.sort_uniform = 0;
   uint64_t *rh = nullptr, *sh = nullptr;
   uint32_t *rr = nullptr, *sr = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_R_HASH, nr, &rh));
@@ -63,11 +65,14 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   HMJ_TRY(hmj_ws(ctx, WS_S_HASH, ns, &sh));
   HMJ_TRY(hmj_ws(ctx, WS_S_ROWID, ns, &sr));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
-  HMJ_TRY(hmj_hash_strings(ctx, d_roffsets, d_rchars, nr, rh));
-  HMJ_TRY(hmj_hash_strings(ctx, d_soffsets, d_schars, ns, sh));
+  uint64_t *rt = nullptr, *st = nullptr;  // unsorted hashes
+  HMJ_TRY(hmj_ws(ctx, WS_HASH_TMP0, nr, &rt));
+  HMJ_TRY(hmj_ws(ctx, WS_HASH_TMP1, ns, &st));
+  HMJ_TRY(hmj_hash_strings(ctx, d_roffsets, d_rchars, nr, rt));
+  HMJ_TRY(hmj_hash_strings(ctx, d_soffsets, d_schars, ns, st));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
-  HMJ_TRY(hmj_sort_pairs(ctx, rh, nullptr, nr, rh, rr));
-  HMJ_TRY(hmj_sort_pairs(ctx, sh, nullptr, ns, sh, sr));
+  HMJ_TRY(hmj_sort_pairs(ctx, rt, nullptr, nr, rh, rr));
+  HMJ_TRY(hmj_sort_pairs(ctx, st, nullptr, ns, sh, sr));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
   hmj_relation R = {rh, rr, nr, HMJ_KEY_STRING, d_roffsets, d_rchars};
   hmj_relation S = {sh, sr, ns, HMJ_KEY_STRING, d_soffsets, d_schars};
@@ -109,12 +114,21 @@ extern "C" int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out) {
   if (cudaEventElapsedTime(&ms, ctx->ev[EV_START], ctx->ev[EV_JOINED]) == cudaSuccess) t.total_ms = ms;
   t.pass_ms_sum = 0;
   t.pass_launches = 0;
+  for (int k = 0; k < 8; ++k) {
+    t.kernel_launches[k] = 0;
+    t.kernel_ms[k] = 0;
+    t.kernel_bytes[k] = 0;
+  }
   for (size_t i = 0; i + 1 < ctx->prof_used; i += 2) {
     if (cudaEventElapsedTime(&ms, ctx->prof_events[i], ctx->prof_events[i + 1]) == cudaSuccess) {
-      t.pass_ms_sum += ms;
-      t.pass_launches++;
+      const int k = ctx->prof_kind[i / 2] & 7;
+      t.kernel_launches[k]++;
+      t.kernel_ms[k] += ms;
+      t.kernel_bytes[k] += ctx->prof_bytes[i / 2];
     }
   }
+  t.pass_ms_sum = t.kernel_ms[HMJ_K_PASS];
+  t.pass_launches = t.kernel_launches[HMJ_K_PASS];
   cudaGetLastError();  // events never recorded yet: not an error for the caller
   *out = t;
   return HMJ_OK;

@@ -99,6 +99,25 @@ constexpr uint64_t LB_STATUS_MASK = 3ull << 62;
 constexpr int LB_EPOCH_SHIFT = 46;
 constexpr uint64_t LB_EPOCH_MASK = 0xFFFFull << LB_EPOCH_SHIFT;
 constexpr uint64_t LB_VALUE_MASK = (1ull << LB_EPOCH_SHIFT) - 1;
+constexpr int LB_WINDOW_DEFAULT = 4;
+
+// Optional per-tile timeline of the pass (scripts/trace_pass.py; compiled only with -DHMJ_TRACE):
+// 12 words per tile = globaltimer at {start, keys loaded, ranked, look-back start, look-back end,
+// scattered, end}, look-back round trips, not-ready polls, SM id.
+#ifdef HMJ_TRACE
+__device__ unsigned long long* g_trace = nullptr;
+__device__ unsigned long long g_trace_tiles = 0;
+__device__ __forceinline__ unsigned long long trace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(slot) do { if (tid == 0 && g_trace && tile < g_trace_tiles) g_trace[(size_t)tile * 12 + (slot)] = trace_now(); } while (0)
+#define TRACE_VAL(slot, v) do { if (tid == 0 && g_trace && tile < g_trace_tiles) g_trace[(size_t)tile * 12 + (slot)] = (v); } while (0)
+#else
+#define TRACE(slot) do {} while (0)
+#define TRACE_VAL(slot, v) do {} while (0)
+#endif
 
 __device__ __forceinline__ void lb_store(uint64_t* p, uint64_t v) {
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -119,7 +138,7 @@ struct OnesweepCfg {
 
 // keys_in/vals_in -> keys_out/vals_out, stable on digit (key >> shift) & 255.
 // vals_in == nullptr means the payload is the element's global index (row id iota).
-template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE>
+template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE, int LB_WINDOW>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
@@ -148,6 +167,7 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
   const uint32_t tile = *s_tile_id;
   const uint32_t tile_base = tile * (uint32_t)TILE;
   const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+  TRACE(0);
 
   // ---- load keys, warp-striped: item k of lane l sits at warp_base + k*32 + l
   const uint32_t warp_base = tile_base + warp * (32 * ITEMS);
@@ -158,6 +178,10 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
     key[k] = (idx < n) ? __ldcs(keys_in + idx) : ~0ull;
   }
 
+#ifdef HMJ_TRACE
+  if (key[ITEMS - 1] == 0x123456789abcdefull) return;  // forces the loads to complete here
+  TRACE(1);
+#endif
   // ---- rank digits inside the warp (stable in item order k, lane)
   uint32_t* whist = s_whist + warp * RADIX;
   uint16_t rank[ITEMS];
@@ -188,20 +212,24 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
             : "r"(d), "r"(1u << b));
       }
     }
+    // the lowest peer adds the group's count to the warp-private bin; shared-memory atomics of
+    // one warp are performed in issue order, so item k+1 sees item k's count without a
+    // __syncwarp and the 16 chains can overlap
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
-    if (lane == leader) {
-      old = whist[d];
-      whist[d] = old + __popc(peers);
-    }
+    if (lane == leader) old = atomicAdd(&whist[d], (uint32_t)__popc(peers));
     old = __shfl_sync(0xffffffffu, old, leader);
     rank[k] = (uint16_t)(old + __popc(peers & lt_mask));
-    __syncwarp();
   }
+  __syncwarp();
   __syncthreads();
 
-  // ---- per digit: exclusive offsets over warps, tile totals, scan over digits, look-back
-  uint32_t count = 0;
+  TRACE(2);
+  // ---- per digit: exclusive offsets over warps, tile totals (published as PARTIAL at once),
+  // scan over digits
+  uint32_t pub = 0, tile_off = 0;
+  const uint64_t tag = (uint64_t)epoch << LB_EPOCH_SHIFT;
+  uint64_t* my_desc = lookback + (size_t)tile * RADIX + (tid & (RADIX - 1));
   if (tid < RADIX) {
     uint32_t sum = 0;
 #pragma unroll
@@ -210,12 +238,10 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
       s_whist[w * RADIX + tid] = sum;
       sum += c;
     }
-    count = sum;
+    const uint32_t count = sum;
     // out-of-range items were given digit 255 and rank last inside it; they are not data.
-    uint32_t pub = count;
+    pub = count;
     if (tid == RADIX - 1) pub -= (uint32_t)TILE - valid;
-    uint64_t* my_desc = lookback + (size_t)tile * RADIX + tid;
-    const uint64_t tag = (uint64_t)epoch << LB_EPOCH_SHIFT;
     if (tile != 0) lb_store(my_desc, LB_PARTIAL | tag | pub);
     // inclusive scan of tile counts across the 256 digits
     uint32_t x = count;
@@ -229,44 +255,70 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
     asm volatile("bar.sync 1, %0;" ::"n"(RADIX));
     uint32_t pre = 0;
     for (int i = 0; i < warp; ++i) pre += s_scan[i];
-    const uint32_t tile_off = pre + x - count;
+    tile_off = pre + x - count;
     s_tile_off[tid] = tile_off;
-    // decoupled look-back over earlier tiles of this digit
+  }
+  __syncthreads();
+
+  // ---- decoupled look-back over earlier tiles of this digit, LB_WINDOW descriptors per round
+  // trip.  Tiles start every ~30 ns while one L2 round trip is several hundred ns, so a serial
+  // walk (one descriptor per trip) cannot keep up once a tile is delayed: the window must cover
+  // the tiles that start during one trip (profiles/r1c: 30 % of the stall samples sat here).
+  TRACE(3);
+  if (tid < RADIX) {
     uint32_t excl = 0;
+    unsigned long long trips = 0, polls = 0;
     if (tile != 0) {
       int64_t prev = (int64_t)tile - 1;
-      while (true) {
-        const uint64_t v = lb_load(lookback + (size_t)prev * RADIX + tid);
-        if ((v & LB_EPOCH_MASK) != tag || (v & LB_STATUS_MASK) == 0) continue;  // not ready
-        excl += (uint32_t)(v & LB_VALUE_MASK);
-        if ((v & LB_STATUS_MASK) == LB_INCLUSIVE) break;
-        --prev;
+      bool done = false;
+      while (!done) {
+        ++trips;
+        uint64_t v[LB_WINDOW];
+#pragma unroll
+        for (int j = 0; j < LB_WINDOW; ++j)
+          v[j] = (prev - j >= 0) ? lb_load(lookback + (size_t)(prev - j) * RADIX + tid) : 0;
+        int used = 0;
+#pragma unroll
+        for (int j = 0; j < LB_WINDOW; ++j) {
+          if (done || used != j) continue;
+          if ((v[j] & LB_EPOCH_MASK) != tag || (v[j] & LB_STATUS_MASK) == 0) continue;  // not ready
+          excl += (uint32_t)(v[j] & LB_VALUE_MASK);
+          ++used;
+          if ((v[j] & LB_STATUS_MASK) == LB_INCLUSIVE) done = true;
+        }
+        prev -= used;
+        if (used == 0) ++polls;
       }
     }
+    TRACE_VAL(7, trips);
+    TRACE_VAL(8, polls);
+    TRACE(4);
     lb_store(my_desc, LB_INCLUSIVE | tag | (uint64_t)(excl + pub));
     s_gbase[tid] = bin_offsets[tid] + excl - tile_off;
   }
+
+  // ---- scatter keys into tile-sorted order in shared memory (tile-local offsets only)
+  {
+    uint16_t pos[ITEMS];
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
+      const uint32_t p = s_tile_off[d] + whist[d] + rank[k];
+      pos[k] = (uint16_t)p;
+      s_keys[p] = key[k];
+    }
+    // payloads (loaded late to keep registers low)
+#pragma unroll
+    for (int k = 0; k < ITEMS; ++k) {
+      const uint32_t idx = warp_base + k * 32 + lane;
+      uint32_t v = idx + iota_base;
+      if (vals_in != nullptr && idx < n) v = __ldcs(vals_in + idx);
+      s_vals[pos[k]] = v;
+    }
+  }
   __syncthreads();
 
-  // ---- scatter keys into tile-sorted order in shared memory
-  uint16_t pos[ITEMS];
-#pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    const uint32_t d = (uint32_t)(key[k] >> shift) & (RADIX - 1);
-    const uint32_t p = s_tile_off[d] + whist[d] + rank[k];
-    pos[k] = (uint16_t)p;
-    s_keys[p] = key[k];
-  }
-  // payloads (loaded late to keep registers low)
-#pragma unroll
-  for (int k = 0; k < ITEMS; ++k) {
-    const uint32_t idx = warp_base + k * 32 + lane;
-    uint32_t v = idx + iota_base;
-    if (vals_in != nullptr && idx < n) v = __ldcs(vals_in + idx);
-    s_vals[pos[k]] = v;
-  }
-  __syncthreads();
-
+  TRACE(5);
   // ---- write out: consecutive threads write consecutive slots of a digit's run
 #pragma unroll 4
   for (uint32_t i = tid; i < valid; i += THREADS) {
@@ -276,9 +328,23 @@ onesweep_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __res
     keys_out[dst] = kk;
     vals_out[dst] = s_vals[i];
   }
+#ifdef HMJ_TRACE
+  TRACE(6);
+  unsigned smid;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  TRACE_VAL(9, (unsigned long long)smid);
+#endif
 }
 
 }  // namespace
+
+#ifdef HMJ_TRACE
+extern "C" int hmj_debug_trace(unsigned long long* d_buf, unsigned long long tiles) {
+  cudaError_t e = cudaMemcpyToSymbol(g_trace, &d_buf, sizeof d_buf);
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_trace_tiles, &tiles, sizeof tiles);
+  return e == cudaSuccess ? 0 : -2;
+}
+#endif
 
 // ---------------------------------------------------------------- host driver
 namespace {
@@ -288,33 +354,22 @@ __global__ void iota_kernel(uint32_t* __restrict__ out, uint32_t n) {
   for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = i;
 }
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE = 0>
+template <int THREADS, int ITEMS, int MIN_BLOCKS, int RANK_MODE = 0, int LBW = LB_WINDOW_DEFAULT>
 int launch_pass(hmj_ctx* ctx, const uint64_t* kin, const uint32_t* vin, uint64_t* kout,
                 uint32_t* vout, uint32_t n, int shift, const uint32_t* bins, uint64_t* lookback,
                 uint32_t* counter, uint32_t epoch, uint32_t iota_base = 0) {
   using Cfg = OnesweepCfg<THREADS, ITEMS>;
   // per-device attribute; cheap enough to set on every launch
-  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE>,
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE, LBW>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)Cfg::SMEM_BYTES));
   const uint32_t tiles = (uint32_t)hmj_div_up(n, Cfg::TILE);
-  cudaEvent_t ev_after = nullptr;
-  if (ctx->prof_on) {
-    if (ctx->prof_used + 2 > ctx->prof_events.size()) {
-      cudaEvent_t a, b;
-      HMJ_CUDA(ctx, cudaEventCreate(&a));
-      HMJ_CUDA(ctx, cudaEventCreate(&b));
-      ctx->prof_events.push_back(a);
-      ctx->prof_events.push_back(b);
-    }
-    HMJ_CUDA(ctx, cudaEventRecord(ctx->prof_events[ctx->prof_used], ctx->stream));
-    ev_after = ctx->prof_events[ctx->prof_used + 1];
-    ctx->prof_used += 2;
-  }
-  onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
+  cudaEvent_t ev_after;
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_PASS, (double)n * (vin ? 24.0 : 20.0), &ev_after));
+  onesweep_pass_kernel<THREADS, ITEMS, MIN_BLOCKS, RANK_MODE, LBW><<<tiles, THREADS, Cfg::SMEM_BYTES, ctx->stream>>>(
       kin, vin, kout, vout, n, shift, bins, lookback, counter, epoch, iota_base);
   HMJ_LAUNCHED(ctx);
-  if (ev_after) HMJ_CUDA(ctx, cudaEventRecord(ev_after, ctx->stream));
+  hmj_prof_end(ctx, ev_after);
   return HMJ_OK;
 }
 
@@ -520,6 +575,19 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   const int tile_items = tile_items_for_cfg(cfg);
   const size_t tiles = hmj_div_up(n, tile_items);
 
+  const int hyb = hybrid_from_env();
+  const uint32_t seg_cap = (uint32_t)hmj_segment_sort_cap();
+  // hashes with implicit row ids: try the uniform-hash path first (no histogram, no stable
+  // passes); it declines or fails on skewed / heavily duplicated keys and leaves the input intact
+  if (vals_in == nullptr && hyb == 2) {
+    int ok = 0;
+    HMJ_TRY(hmj_sort_uniform_try(ctx, keys_in, n, 0, keys_out, vals_out, &ok));
+    if (ok) {
+      ctx->tm.sort_uniform += 1;
+      return HMJ_OK;
+    }
+  }
+
   // scratch: [8*256 bins][16 stats][24 tile counters][8 flags]
   constexpr int MAX_LAUNCHED_PASSES = 24;
   uint32_t* d_hist = nullptr;
@@ -532,8 +600,11 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
 
   const size_t chunk = (size_t)HIST_THREADS * HIST_ITEMS;
   const int hgrid = (int)min(hmj_div_up(n, chunk), (size_t)ctx->num_sms * 4);
+  cudaEvent_t ev_hist;
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_HIST, (double)n * 8.0, &ev_hist));
   radix_histogram_kernel<<<hgrid, HIST_THREADS, 0, st>>>(keys_in, n, d_hist);
   HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev_hist);
   radix_scan_kernel<<<NUM_PASSES, RADIX, 0, st>>>(d_hist, n32, d_stats);
   HMJ_LAUNCHED(ctx);
 
@@ -541,8 +612,6 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   // finish is enough.  Small sorts skip the read-back and run every pass.
   DigitStats stats[NUM_PASSES];
   for (int p = 0; p < NUM_PASSES; ++p) stats[p] = {RADIX, 0};
-  const int hyb = hybrid_from_env();
-  const uint32_t seg_cap = (uint32_t)hmj_segment_sort_cap();
   const bool planned = hyb == 2 ? n > seg_cap : n >= (size_t(1) << 15);
   if (planned) {
     uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
@@ -676,8 +745,8 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
       const uint32_t* bins = d_hist + p * RADIX;
       uint32_t* counter = d_counters + (counter_idx++);
       int rc;
-#define HMJ_PASS(T, I, B, R) \
-  rc = launch_pass<T, I, B, R>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, counter, epoch)
+#define HMJ_PASS(T, I, B, R, ...) \
+  rc = launch_pass<T, I, B, R, ##__VA_ARGS__>(ctx, cur_k, cur_v, dk, dv, n32, p * RADIX_BITS, bins, d_lb, counter, epoch)
       switch (cfg) {
         case 1: HMJ_PASS(256, 16, 3, 1); break;
         case 2: HMJ_PASS(256, 16, 3, 2); break;
@@ -688,6 +757,10 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
         case 7: HMJ_PASS(256, 24, 2, 2); break;
         case 8: HMJ_PASS(384, 16, 2, 1); break;
         case 9: HMJ_PASS(384, 16, 2, 2); break;
+        case 10: HMJ_PASS(256, 16, 3, 0, 1); break;
+        case 11: HMJ_PASS(256, 16, 3, 0, 2); break;
+        case 13: HMJ_PASS(256, 16, 3, 0, 8); break;
+        case 14: HMJ_PASS(256, 16, 3, 0, 16); break;
         default: HMJ_PASS(256, 16, 3, 0); break;
       }
 #undef HMJ_PASS
@@ -722,6 +795,8 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   }
 
   if (finish_shift >= 0) {
+    cudaEvent_t ev_fin;
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_FINISH, (double)n * (finish_kind == 2 ? 24.0 : 8.0), &ev_fin));
     if (finish_kind == 2) {
       HMJ_TRY(hmj_launch_segment_sort(ctx, bufs[where].k, bufs[where].v, n32, 64 - finish_shift,
                                       seg_group_shift, seg_stride, d_flag));
@@ -730,6 +805,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
           bufs[where].k, bufs[where].v, n32, finish_shift, d_flag);
       HMJ_LAUNCHED(ctx);
     }
+    hmj_prof_end(ctx, ev_fin);
     ctx->tm.sort_finishes += 1;
     uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
     HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
@@ -782,9 +858,11 @@ extern "C" int hmj_hash_sort_strings(hmj_ctx* ctx, const uint64_t* d_offsets,
                                      uint32_t* d_rowid_out) {
   if (!ctx) return HMJ_EARG;
   if (n == 0) return HMJ_OK;
-  // hash into the output column, then sort it in place (ping-pong through the workspace)
-  HMJ_TRY(hmj_hash_strings(ctx, d_offsets, d_chars, n, d_hash_out));
-  return hmj_impl_sort(ctx, d_hash_out, nullptr, n, d_hash_out, d_rowid_out);
+  // hash into a scratch column, sort from there into the output columns
+  uint64_t* d_tmp = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_HASH_TMP0, n, &d_tmp));
+  HMJ_TRY(hmj_hash_strings(ctx, d_offsets, d_chars, n, d_tmp));
+  return hmj_impl_sort(ctx, d_tmp, nullptr, n, d_hash_out, d_rowid_out);
 }
 
 // ---------------------------------------------------------------- K8: top-bits partition

@@ -34,10 +34,17 @@ struct SegCfg {
       (size_t)(CAP + 4) * 8 + (size_t)CAP * 4 + (size_t)(SEG_BINS + 1) * 4 + 32 * 4 + 16;
 };
 
-template <int THREADS, int ITEMS, int MIN_BLOCKS>
+// PADDED = false: window w = [win[w], win[w+1]) of (keys, vals), sorted in place; ties keep their
+//   window order (stable).
+// PADDED = true : window w = bucket w of the uniform sort (bucket_scatter.cu): counts[w] pairs at
+//   keys[w * in_cap ...], all sharing the q-bit prefix w; written to out_* at offsets[w]; ties
+//   are ordered by the payload (the row id).
+template <int THREADS, int ITEMS, int MIN_BLOCKS, bool PADDED>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
-                    const uint32_t* __restrict__ win, int q, uint32_t* __restrict__ flag) {
+                    const uint32_t* __restrict__ win, int q, uint32_t* __restrict__ flag,
+                    const uint32_t* __restrict__ counts, uint32_t in_cap,
+                    uint64_t* __restrict__ out_keys, uint32_t* __restrict__ out_vals) {
   using Cfg = SegCfg<THREADS, ITEMS>;
   constexpr int CAP = Cfg::CAP;
   constexpr int PER = (SEG_BINS + THREADS - 1) / THREADS;  // bins scanned per thread
@@ -52,9 +59,24 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
   uint32_t* s_warp = s_bin + SEG_BINS + 1;                // [32]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t start = win[blockIdx.x], end = win[blockIdx.x + 1];
-  if (end <= start + 1) return;  // empty or a single pair: already in place
-  const uint32_t len = end - start;
+  uint32_t start, len, out_start;
+  if (PADDED) {
+    // a scatter level overflowed: counts and offsets mean nothing, the host re-sorts
+    if (*reinterpret_cast<volatile uint32_t*>(flag) != 0) return;
+    len = counts[blockIdx.x];
+    start = blockIdx.x * in_cap;
+    out_start = win[blockIdx.x];
+    if (len == 0) return;
+    if (len > in_cap) return;  // overflowed bucket: the scatter has raised the flag already
+  } else {
+    start = win[blockIdx.x];
+    const uint32_t end = win[blockIdx.x + 1];
+    if (end <= start + 1) return;  // empty or a single pair: already in place
+    len = end - start;
+    out_start = start;
+    out_keys = keys;
+    out_vals = vals;
+  }
   if (len > (uint32_t)CAP) {
     if (tid == 0) atomicOr(flag, 1u);
     return;
@@ -76,8 +98,11 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
   const int pshift = 64 - q;  // q in [0, 56]
   uint64_t base = 0;
   int s;
-  {
-    const uint64_t k_first = keys[start], k_last = keys[end - 1];
+  if (PADDED) {
+    s = max(0, pshift - 12);
+    base = q ? ((uint64_t)blockIdx.x << pshift) : 0;
+  } else {
+    const uint64_t k_first = keys[start], k_last = keys[start + len - 1];
     const uint64_t plo = q ? (k_first >> pshift) : 0, phi = q ? (k_last >> pshift) : 0;
     const uint64_t npre = phi - plo + 1;
     if (npre <= (uint64_t)SEG_BINS) {
@@ -215,8 +240,27 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
   for (int k = 0; k < ITEMS; ++k) {
     const uint32_t i = tid + k * THREADS;
     if (i < len) {
-      keys[start + i] = s_keys[i];
-      vals[start + i] = s_vals[i];
+      const uint64_t kk = s_keys[i];
+      const uint32_t v = s_vals[i];
+      uint32_t at = i;
+      if (PADDED) {
+        // equal keys arrived in no particular order: a run of them is ordered by row id
+        const bool left = i > 0 && s_keys[i - 1] == kk, right = i + 1 < len && s_keys[i + 1] == kk;
+        if (left || right) {
+          uint32_t a = i, b = i + 1, r = 0;
+          while (a > 0 && s_keys[a - 1] == kk) {
+            --a;
+            r += s_vals[a] < v ? 1u : 0u;
+          }
+          while (b < len && s_keys[b] == kk) {
+            r += s_vals[b] < v ? 1u : 0u;
+            ++b;
+          }
+          at = a + r;
+        }
+      }
+      out_keys[out_start + i] = kk;
+      out_vals[out_start + at] = v;
     }
   }
 }
@@ -302,10 +346,26 @@ int hmj_launch_segment_sort(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, uint32
   segment_windows_kernel<<<(nwin + 1 + 255) / 256, 256, 0, st>>>(
       keys, n, q, stride, group_shift, (uint32_t)SegDefault::CAP + 2, nwin, d_win);
   HMJ_LAUNCHED(ctx);
-  auto kern = segment_sort_kernel<512, 9, 2>;
+  auto kern = segment_sort_kernel<512, 9, 2, false>;
   HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)SegDefault::SMEM_BYTES));
-  kern<<<nwin, 512, SegDefault::SMEM_BYTES, st>>>(keys, vals, d_win, q, d_flag);
+  kern<<<nwin, 512, SegDefault::SMEM_BYTES, st>>>(keys, vals, d_win, q, d_flag, nullptr, 0, nullptr,
+                                                  nullptr);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
+}
+
+// Finish of the uniform sort: bucket w (counts[w] pairs at slot w * in_cap of the padded
+// columns, common q-bit prefix w) is sorted and written to out_* at offsets[w].
+int hmj_launch_bucket_finish(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, const uint32_t* counts,
+                             const uint32_t* offsets, uint32_t buckets, uint32_t in_cap, int q,
+                             uint64_t* out_keys, uint32_t* out_vals, uint32_t* d_flag) {
+  HMJ_ARG(ctx, q >= 0 && q <= 32 && in_cap <= (uint32_t)SegDefault::CAP);
+  auto kern = segment_sort_kernel<512, 9, 2, true>;
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)SegDefault::SMEM_BYTES));
+  kern<<<buckets, 512, SegDefault::SMEM_BYTES, ctx->stream>>>(keys, vals, offsets, q, d_flag, counts,
+                                                              in_cap, out_keys, out_vals);
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }

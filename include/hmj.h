@@ -191,7 +191,20 @@ typedef struct hmj_timings {
   uint32_t pass_launches;
   uint32_t sort_finishes;  /* bucket-finish launches (prefix sort + small-bucket finish) */
   uint32_t sort_fallbacks; /* sorts that met an oversized bucket and re-ran with scatter passes */
+  uint32_t sort_uniform;   /* sorts completed by the uniform-hash path (bucket scatter + finish) */
+  /* per kernel class (hmj_kernel_class), accumulated while profiling is on */
+  uint32_t kernel_launches[8];
+  float kernel_ms[8];
+  double kernel_bytes[8]; /* algorithmic bytes of the timed launches */
 } hmj_timings;
+enum hmj_kernel_class {
+  HMJ_K_PASS = 0,    /* onesweep_pass_kernel (stable scatter pass) */
+  HMJ_K_SCATTER = 1, /* bucket_scatter_kernel (uniform-hash levels) */
+  HMJ_K_FINISH = 2,  /* segment_sort_kernel / bucket_finish_kernel */
+  HMJ_K_JOIN = 3,    /* join_tile_kernel */
+  HMJ_K_HIST = 4,    /* radix_histogram_kernel */
+  HMJ_K_HASH = 5     /* hash_strings_kernel */
+};
 int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
 /* on != 0: bracket every onesweep-pass launch with CUDA events on the context's stream and
  * reset the accumulated figures; 0: stop.  Used by bench.py for the roofline of the dominant

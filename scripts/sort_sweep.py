@@ -64,9 +64,10 @@ def main():
         pms = tm["pass_ms_sum"] / pl
         print(json.dumps({"var": args.var, "cfg": cfg, "dist": args.dist, "n": n, "ok": ok,
                           "ms_per_sort": round(ms, 4), "passes_per_sort": pl / args.reps,
-                          "ms_per_pass": round(pms, 4), "gbps_per_pass": round(n * 24 / pms / 1e6, 1),
+                          "ms_per_pass": round(pms, 4), "gbps_per_pass": round(n * 24 / pms / 1e6, 1) if pms > 0 else None,
                           "mkeys_per_s": round(n / ms / 1e3, 1), "finishes": tm["sort_finishes"],
-                          "fallbacks": tm["sort_fallbacks"]}), flush=True)
+                          "fallbacks": tm["sort_fallbacks"], "uniform": tm["sort_uniform"],
+                          "kernel_ms_per_sort": [round(x / args.reps, 3) for x in tm["kernel_ms"][:5]]}), flush=True)
     ctx.close()
 
 

@@ -138,7 +138,8 @@ def fast_check_sort(ctx, keys, rowid=None, inplace=False):
     return ctx.timings()
 
 
-def test_sort_hybrid_prefix_and_bucket_finish(ctx):
+def test_sort_hybrid_prefix_and_bucket_finish(ctx, monkeypatch):
+    monkeypatch.setenv("HMJ_SORT_UNIFORM", "0")  # the histogram-planned path is the subject here
     # uniform keys, n >= 2^21: 3 scatter passes on the top 24 bits + bucket finish (shift 40)
     rng = np.random.default_rng(21)
     n = (1 << 21) + 12345
@@ -154,7 +155,8 @@ def test_sort_hybrid_prefix_and_bucket_finish(ctx):
     fast_check_sort(ctx, rng.integers(0, 2 ** 64, size=1 << 17, dtype=np.uint64))
 
 
-def test_sort_hybrid_tie_slow_path(ctx):
+def test_sort_hybrid_tie_slow_path(ctx, monkeypatch):
+    monkeypatch.setenv("HMJ_SORT_UNIFORM", "0")  # the histogram-planned path is the subject here
     # bucket-mates that agree on the 31 bits below the 24-bit prefix and differ only in the low
     # 9 bits: the 32-bit fast ranking cannot order them, the tile must take the full-key path
     rng = np.random.default_rng(22)
@@ -171,7 +173,8 @@ def test_sort_hybrid_tie_slow_path(ctx):
     fast_check_sort(ctx, keys)
 
 
-def test_sort_hybrid_oversized_bucket_falls_back(ctx):
+def test_sort_hybrid_oversized_bucket_falls_back(ctx, monkeypatch):
+    monkeypatch.setenv("HMJ_SORT_UNIFORM", "0")  # the histogram-planned path is the subject here
     # digit histograms look uniform (1200 extra rows in a bin of 32768 is inside the planner's
     # tolerance), but 1200 rows share one 24-bit prefix: the bucket finish flags it and the sort
     # re-runs with scatter passes over every digit -- same result
@@ -187,6 +190,55 @@ def test_sort_hybrid_oversized_bucket_falls_back(ctx):
     # 1200 copies of ONE key (a moderate heavy hitter the histogram test cannot see)
     keys[hot] = np.uint64(0x123456789ABCDEF0)
     fast_check_sort(ctx, keys)
+
+
+# ---- uniform-hash path (bucket_scatter.cu + padded segment sort): iota row ids, no histogram
+@pytest.mark.parametrize("n", [4609, 5000, 100003, (1 << 20) + 5, (1 << 21) + 12345, 1 << 23])
+def test_sort_uniform_path_random(ctx, n):
+    rng = np.random.default_rng(n)
+    keys = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    u0 = ctx.timings()["sort_uniform"]
+    tm = fast_check_sort(ctx, keys)
+    assert tm["sort_uniform"] == u0 + 1, "the uniform path did not run"
+
+
+def test_sort_uniform_path_duplicates_are_ordered_by_row_id(ctx):
+    rng = np.random.default_rng(31)
+    n = 1 << 21
+    base = rng.integers(0, 2 ** 64, size=n // 4, dtype=np.uint64)
+    keys = np.concatenate([base, base, base, base])[rng.permutation(n)]  # every key four times
+    u0 = ctx.timings()["sort_uniform"]
+    tm = fast_check_sort(ctx, keys)
+    assert tm["sort_uniform"] == u0 + 1
+    # runs of 40 equal keys
+    base = rng.integers(0, 2 ** 64, size=n // 40, dtype=np.uint64)
+    keys = np.repeat(base, 40)[rng.permutation(base.size * 40)]
+    fast_check_sort(ctx, keys)
+    # keys that differ only in their low bits inside a bucket
+    top = rng.integers(0, 1 << 20, size=n, dtype=np.uint64) << np.uint64(44)
+    fast_check_sort(ctx, top | rng.integers(0, 512, size=n, dtype=np.uint64))
+
+
+def test_sort_uniform_path_declines_or_recovers(ctx):
+    rng = np.random.default_rng(32)
+    n = 1 << 22
+    # skewed: everything in one top-level bucket -> overflow flag -> histogram-planned sort
+    u0 = ctx.timings()["sort_uniform"]
+    tm = fast_check_sort(ctx, rng.integers(0, 1 << 40, size=n, dtype=np.uint64))
+    assert tm["sort_uniform"] == u0
+    # one final bucket too full (1200 extra rows share a 24-bit prefix)
+    keys = rng.integers(0, 2 ** 64, size=n, dtype=np.uint64)
+    hot = rng.choice(n, size=1200, replace=False)
+    keys[hot] = (np.uint64(0xABCDEF) << np.uint64(40)) | rng.integers(0, 1 << 40, size=1200, dtype=np.uint64)
+    fast_check_sort(ctx, keys)
+    # 1200 copies of one key: a crowded bin inside the bucket
+    keys[hot] = np.uint64(0x123456789ABCDEF0)
+    fast_check_sort(ctx, keys)
+    # explicit payloads never take the uniform path (it orders ties by row id)
+    u0 = ctx.timings()["sort_uniform"]
+    tm = fast_check_sort(ctx, rng.integers(0, 2 ** 64, size=n, dtype=np.uint64),
+                         rowid=rng.permutation(n).astype(np.uint32))
+    assert tm["sort_uniform"] == u0
 
 
 def test_sort_hybrid_small_whole_array_bucket(ctx):
