@@ -137,6 +137,204 @@ bucket_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
   }
 }
 
+// ---- TMA-pipelined variant -------------------------------------------------------------
+// Same algorithm, persistent CTAs (two per SM).  A tile's key and row-id columns arrive in shared
+// memory by 1-D bulk async copies (cp.async.bulk, completion on an mbarrier); the copy of the
+// NEXT tile is issued before the current one is processed, so ~96 KB of loads per SM are always
+// in flight and no thread holds registers for them (the plain kernel above exposes the row-id
+// load latency: profiles/r1d, 54 % of its stall samples).  The tile is permuted in place in its
+// buffer and leaves with coalesced stores.
+constexpr int UT_THREADS = 512;
+constexpr int UT_ITEMS = 8;
+constexpr int UT_TILE = UT_THREADS * UT_ITEMS;  // 4096, must equal US_TILE (same tile grid)
+static_assert(UT_TILE == US_TILE, "tile grids must agree");
+constexpr size_t UT_BUF_BYTES = (size_t)UT_TILE * 12;
+constexpr size_t UT_SMEM = 2 * UT_BUF_BYTES + 3 * US_MAX_BINS * 4 + 32 * 4 + 64;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint32_t bytes,
+                                          uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+__global__ void __launch_bounds__(UT_THREADS, 2)
+bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                          const uint32_t* __restrict__ in_counts, uint32_t in_stride,
+                          uint32_t n_single, uint32_t tiles_per_region, uint32_t total_tiles,
+                          uint32_t iota_base, uint64_t* __restrict__ keys_out,
+                          uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
+                          uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + 2 * UT_BUF_BYTES);
+  uint32_t* s_off = s_cnt + US_MAX_BINS;
+  uint32_t* s_gbase = s_off + US_MAX_BINS;
+  uint32_t* s_scan = s_gbase + US_MAX_BINS;  // [32]
+  uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_scan + 32);  // [2]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int bins = 1 << bits;
+  const uint32_t mask = (uint32_t)bins - 1;
+  if (tid == 0) {
+    mbar_init(&s_bar[0], 1);
+    mbar_init(&s_bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  // tile t -> (region, first pair, number of pairs); 0 pairs = nothing there
+  auto tile_of = [&](uint32_t t, uint32_t* in_base) -> uint32_t {
+    const uint32_t r = t / tiles_per_region, j = t % tiles_per_region;
+    const uint32_t count = in_counts ? min(in_counts[r * US_CURSOR_STRIDE], in_stride) : n_single;
+    const uint64_t first = (uint64_t)j * UT_TILE;
+    if (first >= count) return 0;
+    *in_base = r * in_stride + (uint32_t)first;
+    return (uint32_t)min((uint64_t)UT_TILE, count - first);
+  };
+  // Starts the copies of tile t into buffer b (full tiles only; a partial tile is loaded with
+  // plain loads when its turn comes).  Every thread learns whether a copy is in flight, thread 0
+  // issues it.
+  auto issue = [&](uint32_t t, int b) -> bool {
+    uint32_t in_base = 0;
+    const uint32_t valid = t < total_tiles ? tile_of(t, &in_base) : 0;
+    if (valid != (uint32_t)UT_TILE) return false;
+    if (tid == 0) {
+      unsigned char* buf = smem_raw + (size_t)b * UT_BUF_BYTES;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      const uint32_t bytes = UT_TILE * 8 + (vals_in ? UT_TILE * 4 : 0);
+      mbar_expect_tx(&s_bar[b], bytes);
+      bulk_load(buf, keys_in + in_base, UT_TILE * 8, &s_bar[b]);
+      if (vals_in) bulk_load(buf + UT_TILE * 8, vals_in + in_base, UT_TILE * 4, &s_bar[b]);
+    }
+    return true;
+  };
+
+  uint32_t phase[2] = {0, 0};
+  bool pending_next = issue(blockIdx.x, 0);
+  int it = 0;
+  for (uint32_t t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    const int b = it & 1;
+    const bool pending_cur = pending_next;
+    pending_next = issue(t + gridDim.x, b ^ 1);
+    uint32_t in_base = 0;
+    const uint32_t valid = tile_of(t, &in_base);
+    if (valid == 0) continue;
+    if (__syncthreads_or(tid == 0 && *reinterpret_cast<volatile uint32_t*>(flag) != 0)) {
+      // never leave with a bulk copy still writing into this CTA's shared memory
+      if (pending_cur) mbar_wait(&s_bar[b], phase[b]);
+      if (pending_next) mbar_wait(&s_bar[b ^ 1], phase[b ^ 1]);
+      return;
+    }
+    uint64_t* b_keys = reinterpret_cast<uint64_t*>(smem_raw + (size_t)b * UT_BUF_BYTES);
+    uint32_t* b_vals = reinterpret_cast<uint32_t*>(b_keys + UT_TILE);
+    if (tid < bins) s_cnt[tid] = 0;
+    if (pending_cur) {
+      mbar_wait(&s_bar[b], phase[b]);
+      phase[b] ^= 1;
+    } else {
+      for (uint32_t i = tid; i < valid; i += UT_THREADS) {
+        b_keys[i] = keys_in[in_base + i];
+        if (vals_in) b_vals[i] = vals_in[in_base + i];
+      }
+    }
+    __syncthreads();
+
+    uint64_t key[UT_ITEMS];
+    uint16_t slot[UT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < UT_ITEMS; ++k) {
+      const uint32_t i = tid + k * UT_THREADS;
+      if (i < valid) {
+        key[k] = b_keys[i];
+        slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+      }
+    }
+    __syncthreads();
+
+    uint32_t c = 0, old = 0, bucket = 0;
+    if (tid < bins) {
+      c = s_cnt[tid];
+      bucket = ((t / tiles_per_region) << bits) | (uint32_t)tid;
+      if (c) old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
+    }
+    uint32_t val[UT_ITEMS];
+#pragma unroll
+    for (int k = 0; k < UT_ITEMS; ++k) {
+      const uint32_t i = tid + k * UT_THREADS;
+      if (i < valid) val[k] = vals_in ? b_vals[i] : in_base + i + iota_base;
+    }
+    {
+      uint32_t x = c;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      if (lane == 31) s_scan[warp] = x;
+      __syncthreads();
+      uint32_t wt = lane < warp ? s_scan[lane] : 0;  // 16 warps
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+      if (tid < bins) s_off[tid] = wt + x - c;
+    }
+    __syncthreads();  // s_off ready; every thread holds its keys and row ids in registers
+
+#pragma unroll
+    for (int k = 0; k < UT_ITEMS; ++k) {
+      const uint32_t i = tid + k * UT_THREADS;
+      if (i < valid) {
+        const uint32_t p = s_off[(uint32_t)(key[k] >> shift) & mask] + slot[k];
+        b_keys[p] = key[k];
+        b_vals[p] = val[k];
+      }
+    }
+    bool over = false;
+    if (tid < bins) {
+      over = c != 0 && (old > out_cap || c > out_cap - old);
+      s_gbase[tid] = bucket * out_cap + old - s_off[tid];
+    }
+    if (__syncthreads_or(over)) {
+      if (tid == 0) atomicOr(flag, 1u);
+      if (pending_next) mbar_wait(&s_bar[b ^ 1], phase[b ^ 1]);
+      return;
+    }
+#pragma unroll 4
+    for (uint32_t i = tid; i < valid; i += UT_THREADS) {
+      const uint64_t kk = b_keys[i];
+      const uint32_t dst = s_gbase[(uint32_t)(kk >> shift) & mask] + i;
+      keys_out[dst] = kk;
+      vals_out[dst] = b_vals[i];
+    }
+    __syncthreads();  // the buffer may be refilled from here on
+  }
+}
+
 // exclusive scan of the final bucket counts -> dense output offsets (one CTA; <= 2^18 buckets)
 __global__ void __launch_bounds__(1024)
 bucket_offsets_kernel(const uint32_t* __restrict__ counts, uint32_t buckets,
@@ -247,22 +445,38 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
   }
   HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UT_SMEM));
+  // bulk copies need 16-byte aligned sources (tile starts are multiples of 4096 pairs)
+  const bool tma = uniform_from_env() != 2 && (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0;
+  const uint32_t pgrid = (uint32_t)ctx->num_sms * 2;
   cudaEvent_t ev;
   // level 1: the raw key column -> 2^bits[0] regions
   const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);
   HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
-  bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
-      keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
-      p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0], p.levels == 2 ? p.cap1 : p.cap_seg,
-      d_cur1, d_flag);
+  if (tma)
+    bucket_scatter_tma_kernel<<<min(tiles, pgrid), UT_THREADS, UT_SMEM, st>>>(
+        keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
+        p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0],
+        p.levels == 2 ? p.cap1 : p.cap_seg, d_cur1, d_flag);
+  else
+    bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
+        keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
+        p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0],
+        p.levels == 2 ? p.cap1 : p.cap_seg, d_cur1, d_flag);
   HMJ_LAUNCHED(ctx);
   hmj_prof_end(ctx, ev);
   if (p.levels == 2) {
     const uint32_t tpr = (uint32_t)hmj_div_up(p.cap1, US_TILE);
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
-    bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
-        d_k1, d_v1, d_cur1, p.cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg, d_cur2,
-        d_flag);
+    if (tma)
+      bucket_scatter_tma_kernel<<<min(regions1 * tpr, pgrid), UT_THREADS, UT_SMEM, st>>>(
+          d_k1, d_v1, d_cur1, p.cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1],
+          p.cap_seg, d_cur2, d_flag);
+    else
+      bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
+          d_k1, d_v1, d_cur1, p.cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg,
+          d_cur2, d_flag);
     HMJ_LAUNCHED(ctx);
     hmj_prof_end(ctx, ev);
   }
