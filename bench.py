@@ -98,12 +98,13 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic(alg_bytes):
-    """dram__bytes_read.sum + dram__bytes_write.sum per onesweep launch from the committed
+def ncu_traffic(kernel, alg_bytes):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
     `ncu --set full` capture (profiles/roofline_traffic.json), scaled from the captured launch's
     pair count to this run's by the ratio of algorithmic bytes; None when no capture exists."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+        t = t["kernels"][kernel]
         return t["dram_bytes_per_launch"] * alg_bytes / t["algorithmic_bytes_per_launch"]
     except Exception:
         return None
@@ -253,29 +254,28 @@ def run_gpu(args):
     ms_per_step = elapsed_ms / args.steps
     value = 2 * rows_total / (ms_per_step * 1e-3)
 
-    # ---- roofline of the dominant kernel (onesweep scatter pass), timed per launch with CUDA
-    # events on the launching stream during the timed steps (hmj_set_profiling)
+    # ---- roofline of the dominant kernel class, timed per launch with CUDA events on the
+    # launching stream during the timed steps (hmj_set_profiling).  Algorithmic bytes per launch
+    # are accumulated by the library at the launch sites.
     peak, peak_src = peaks()
-    pass_launches = max(tm["pass_launches"], 1)
-    avg_pass_ms = tm["pass_ms_sum"] / pass_launches
-    passes_per_sort = pass_launches / (2.0 * args.steps)
-    if world == 1:
-        # per launch: 12 B read + 12 B written per pair; the first pass of each sort reads only
-        # the 8-byte keys (row ids are generated, not loaded)
-        alg_bytes = rows * (24.0 - 4.0 / passes_per_sort)
-    else:
-        # pairs arrive from the exchange with explicit row ids: every pass moves 24 B per pair;
-        # the partition pass (K8) over the local block reads 8 and writes 12
-        nr_loc, ns_loc = joiner.local_rows
-        sort_launches = pass_launches - 2 * args.steps
-        alg_bytes = ((nr_loc + ns_loc) / 2.0 * 24.0 * sort_launches + rows * 20.0 * 2 * args.steps) / pass_launches
-    achieved = alg_bytes / (avg_pass_ms * 1e-3) / 1e9 if avg_pass_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "onesweep_pass_kernel", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(alg_bytes),
-                "peak_source": peak_src, "algorithmic_bytes_per_launch": alg_bytes,
-                "avg_launch_ms": avg_pass_ms, "launches_timed": tm["pass_launches"],
-                "passes_per_sort": passes_per_sort,
-                "share_of_step": tm["pass_ms_sum"] / elapsed_ms if elapsed_ms else None}
+    names = ["onesweep_pass_kernel", "bucket_scatter_tma_kernel", "segment_sort_kernel",
+             "join_tile_kernel", "radix_histogram_kernel", "hash_strings_kernel"]
+    kernels = {}
+    for i, nm in enumerate(names):
+        ln, ms_sum, by = tm["kernel_launches"][i], tm["kernel_ms"][i], tm["kernel_bytes"][i]
+        if ln:
+            kernels[nm] = {"launches": ln, "avg_ms": ms_sum / ln, "alg_bytes_per_launch": by / ln,
+                           "gbps": by / ms_sum / 1e6 if ms_sum > 0 else None,
+                           "share_of_step": ms_sum / elapsed_ms if elapsed_ms else None}
+    top = max(kernels, key=lambda k: kernels[k]["share_of_step"]) if kernels else None
+    roofline = None
+    if top:
+        k = kernels[top]
+        roofline = {"bound": "hbm", "kernel": top, "achieved": k["gbps"], "peak": peak, "unit": "GB/s",
+                    "frac": k["gbps"] / peak, "traffic": ncu_traffic(top, k["alg_bytes_per_launch"]),
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": k["alg_bytes_per_launch"],
+                    "avg_launch_ms": k["avg_ms"], "launches_timed": k["launches"],
+                    "share_of_step": k["share_of_step"], "kernels": kernels}
 
     # ---- e2e: host buffers through the C ABI (H2D + join + D2H of the pairs), N=1 only here
     e2e = None
@@ -356,7 +356,7 @@ def run_gpu(args):
                        "key": "u64 (splitmix64 of a row permutation; same key set both sides)",
                        "l2": "inputs (2 x %.1f GB) and every intermediate exceed the 126 MB L2; no flush needed" % (rows * 8 / 1e9),
                        "sort_passes_per_join": tm["sort_passes"], "bucket_finishes_per_join": tm["sort_finishes"],
-                       "sort_fallbacks": tm["sort_fallbacks"],
+                       "sort_fallbacks": tm["sort_fallbacks"], "uniform_sorts_per_join": tm["sort_uniform"],
                        "parallelism": "hash-range partition x%d" % world},
             "stage_ms_last_step": {k: tm[k] for k in ("hash_ms", "sort_ms", "join_ms", "total_ms")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,

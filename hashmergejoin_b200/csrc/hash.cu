@@ -97,8 +97,11 @@ extern "C" int hmj_hash_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const u
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   const size_t tiles = hmj_div_up(n, HASH_TILE_ROWS);
   const int grid = (int)min(tiles, (size_t)ctx->num_sms * 16);
+  cudaEvent_t ev;  // 8 (offset) + 8 (hash) per row; the key bytes are added by whoever knows them
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_HASH, (double)n * 16.0, &ev));
   hash_strings_kernel<<<grid, HASH_THREADS, 0, ctx->stream>>>(d_offsets, d_chars, n, d_hash);
   HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev);
   return HMJ_OK;
 }
 

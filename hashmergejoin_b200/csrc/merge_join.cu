@@ -684,6 +684,8 @@ int join_plan(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s, JoinPl
 template <int MODE>
 int launch_tiles(hmj_ctx* ctx, const JoinPlan& plan) {
   if (plan.args.tiles == 0) return HMJ_OK;
+  cudaEvent_t ev;  // algorithmic bytes: 12 per input tuple here, + 8 per pair once the count is known
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_JOIN, ((double)plan.args.nr + plan.args.ns) * (MODE == JOIN_COUNT ? 8.0 : 12.0), &ev));
   if (plan.kind == HMJ_KEY_U64) {
     HMJ_CUDA(ctx, cudaFuncSetAttribute(join_tile_kernel<HMJ_KEY_U64, MODE>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JOIN_SMEM_BASE));
@@ -694,6 +696,7 @@ int launch_tiles(hmj_ctx* ctx, const JoinPlan& plan) {
     join_tile_kernel<HMJ_KEY_STRING, MODE><<<plan.args.tiles, JOIN_THREADS, JOIN_SMEM_STR, ctx->stream>>>(plan.args);
   }
   HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev);
   return HMJ_OK;
 }
 
@@ -730,6 +733,8 @@ int join_fused(hmj_ctx* ctx, JoinPlan* plan, uint32_t* d_out_r, uint32_t* d_out_
   HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.agg + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
   HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *h_total = h[0];
+  if (ctx->prof_on && ctx->prof_used >= 2 && h[0] <= cap)
+    ctx->prof_bytes[ctx->prof_used / 2 - 1] += 8.0 * (double)h[0];
   return HMJ_OK;
 }
 
