@@ -1,0 +1,341 @@
+// bucket_join.cu -- K6u: the join of two relations that were scattered into the SAME hash-prefix
+// buckets by the uniform path (bucket_scatter.cu), without materialising the sorted columns.
+//
+// The reference sorts both relations completely and then walks the two sorted hash streams
+// (hashjoin.h:56-68, 70-180).  Once both relations are cut on the same top hash bits, bucket b of
+// R can only match bucket b of S, and a bucket pair (~2 x 4096 pairs) fits in shared memory.  A
+// CTA therefore finishes the ordering of S's bucket on the next 12 hash bits in shared memory
+// (counting sort, as segment_sort.cu), lets every R pair look at the 1-2 S pairs of its bin,
+// compares the full 64-bit hashes (and, for strings, the keys: hashjoin.h:139-141) and emits
+// (build_row, probe_row).  That removes the write of both sorted relations (12 B per tuple), their
+// re-read by the merge join (12 B per tuple) and the merge-path search.
+// Output: pairs of bucket b come before those of bucket b+1 (ascending hash prefix; offsets from
+// a decoupled look-back over per-bucket totals, as merge_join.cu), staged in shared memory and
+// written with coalesced stores.  Inside a bucket the order follows the arrival order of the
+// scatter and is not specified (the reference leaves the order of equal hashes unspecified too).
+// Algorithmic bytes: 12 per input tuple + 8 per output pair.
+#include "common.cuh"
+#include "join_device.cuh"
+
+namespace {
+
+constexpr int BJ_THREADS = 512;
+constexpr int BJ_ITEMS = 9;
+constexpr int BJ_CAP = BJ_THREADS * BJ_ITEMS;  // == hmj_segment_sort_cap()
+constexpr int BJ_BINS = 4096;
+constexpr int BJ_PER = BJ_BINS / BJ_THREADS;
+constexpr size_t BJ_SMEM = (size_t)BJ_CAP * 8 + (size_t)BJ_CAP * 4 + (size_t)(BJ_BINS + 1) * 4 +
+                           2 * (size_t)BJ_CAP * 4 + 64 * 8 + 64;
+
+constexpr uint64_t BD_PARTIAL = 1ull << 62;
+constexpr uint64_t BD_INCLUSIVE = 2ull << 62;
+constexpr uint64_t BD_VALUE = (1ull << 62) - 1;
+
+struct BJArgs {
+  const uint64_t* rk; const uint32_t* rv; const uint32_t* rcnt; const uint32_t* rflag;
+  const uint64_t* sk; const uint32_t* sv; const uint32_t* scnt; const uint32_t* sflag;
+  uint32_t in_cap, buckets;
+  int q;
+  const uint64_t* roff; const uint8_t* rchars;  // string key storage (row-id indexed)
+  const uint64_t* soff; const uint8_t* schars;
+  uint32_t* out_r; uint32_t* out_s;
+  uint64_t cap;            // capacity of out_r / out_s in pairs
+  uint64_t* desc;          // [buckets] look-back descriptors (zeroed)
+  uint32_t* counter;       // dynamic bucket ids (zeroed)
+  uint64_t* total;         // number of pairs of the whole join
+};
+
+__device__ __forceinline__ void bd_store(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t bd_load(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(BJ_THREADS, 2)
+bucket_join_kernel(const BJArgs A) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);   // S hashes, grouped by bin
+  uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + BJ_CAP);
+  uint32_t* s_bin = s_vals + BJ_CAP;                          // [BINS + 1]
+  uint32_t* s_or = s_bin + BJ_BINS + 1;                       // staged output pairs
+  uint32_t* s_os = s_or + BJ_CAP;
+  uint64_t* s_tmp = reinterpret_cast<uint64_t*>(
+      (reinterpret_cast<uintptr_t>(s_os + BJ_CAP) + 7) & ~uintptr_t(7));  // [64]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+  if (tid == 0) s_tmp[40] = atomicAdd(A.counter, 1u);
+  __syncthreads();
+  const uint32_t b = (uint32_t)s_tmp[40];
+  // a scatter level overflowed somewhere: the buckets are void, the host takes the other path
+  const bool dead = *reinterpret_cast<const volatile uint32_t*>(A.rflag) != 0 ||
+                    *reinterpret_cast<const volatile uint32_t*>(A.sflag) != 0;
+  if (dead) return;
+  const uint32_t nr = min(A.rcnt[b], A.in_cap), ns = min(A.scnt[b], A.in_cap);
+  const uint32_t base_slot = b * A.in_cap;
+
+  // ---- both buckets into registers
+  uint64_t rkey[BJ_ITEMS], skey[BJ_ITEMS];
+  uint32_t rrow[BJ_ITEMS], srow[BJ_ITEMS];
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    if (i < ns) {
+      skey[k] = A.sk[base_slot + i];
+      srow[k] = A.sv[base_slot + i];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    if (i < nr) {
+      rkey[k] = A.rk[base_slot + i];
+      rrow[k] = A.rv[base_slot + i];
+    }
+  }
+  for (int i = tid; i <= BJ_BINS; i += BJ_THREADS) s_bin[i] = 0;
+  const int pshift = 64 - A.q;
+  const int s = max(0, pshift - 12);
+  const uint64_t kbase = (uint64_t)b << pshift;
+  __syncthreads();
+
+  // ---- S: counting sort on the 12 bits below the prefix
+  uint16_t slot[BJ_ITEMS];
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    if (i < ns) slot[k] = (uint16_t)atomicAdd(&s_bin[(uint32_t)((skey[k] - kbase) >> s)], 1u);
+  }
+  __syncthreads();
+  {
+    uint32_t c[BJ_PER], sum = 0;
+#pragma unroll
+    for (int j = 0; j < BJ_PER; ++j) {
+      c[j] = s_bin[tid * BJ_PER + j];
+      sum += c[j];
+    }
+    uint32_t x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    uint32_t* s_w = reinterpret_cast<uint32_t*>(s_tmp);
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    uint32_t wt = lane < warp ? s_w[lane] : 0;  // 16 warps
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+    uint32_t pre = wt + x - sum;
+#pragma unroll
+    for (int j = 0; j < BJ_PER; ++j) {
+      s_bin[tid * BJ_PER + j] = pre;
+      pre += c[j];
+    }
+    if (tid == 0) s_bin[BJ_BINS] = ns;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    if (i < ns) {
+      const uint32_t p = s_bin[(uint32_t)((skey[k] - kbase) >> s)] + slot[k];
+      s_keys[p] = skey[k];
+      s_vals[p] = srow[k];
+    }
+  }
+  __syncthreads();
+
+  // ---- R probes: matches of every R pair among the S pairs of its bin
+  auto match = [&](uint64_t key, uint32_t row, uint32_t j) -> bool {
+    if (s_keys[j] != key) return false;
+    if (KIND == HMJ_KEY_U64) return true;
+    return keys_equal_str(A.roff, A.rchars, row, A.soff, A.schars, s_vals[j]);
+  };
+  uint32_t mine = 0;
+  uint16_t cnt[BJ_ITEMS];
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    cnt[k] = 0;
+    if (i < nr) {
+      const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+      const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
+      uint32_t c = 0;
+      for (uint32_t j = b0; j < b1; ++j) c += match(rkey[k], rrow[k], j) ? 1u : 0u;
+      cnt[k] = (uint16_t)c;  // a bin holds <= CAP pairs
+      mine += c;
+    }
+  }
+  // exclusive scan of the per-thread totals (thread-major order of the output)
+  uint32_t t_off, tile_total;
+  {
+    uint32_t x = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    uint32_t* s_w = reinterpret_cast<uint32_t*>(s_tmp);
+    __syncthreads();
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    uint32_t wt = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < BJ_THREADS / 32; ++w) {
+      const uint32_t t = s_w[w];
+      if (w < warp) wt += t;
+      tot += t;
+    }
+    t_off = wt + x - mine;
+    tile_total = tot;
+  }
+
+  // ---- global offset of the bucket: decoupled look-back, one warp, 32 descriptors per trip
+  if (warp == 0) {
+    const uint64_t mine64 = tile_total;
+    if (lane == 0 && b != 0) bd_store(A.desc + b, BD_PARTIAL | mine64);
+    uint64_t excl = 0;
+    int64_t first_idx = (int64_t)b - 1;
+    while (first_idx >= 0) {
+      const int64_t idx = first_idx - lane;
+      uint64_t d = BD_INCLUSIVE;  // before bucket 0: an inclusive prefix of zero
+      if (idx >= 0) {
+        d = bd_load(A.desc + idx);
+        while ((d >> 62) == 0) d = bd_load(A.desc + idx);
+      }
+      const uint32_t incl = __ballot_sync(0xffffffffu, (d >> 62) == 2);
+      const int stop = incl ? (__ffs(incl) - 1) : 31;
+      uint64_t c = (lane <= stop) ? (d & BD_VALUE) : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+      excl += c;
+      if (incl) break;
+      first_idx -= 32;
+    }
+    if (lane == 0) {
+      bd_store(A.desc + b, BD_INCLUSIVE | (excl + mine64));
+      if (b == A.buckets - 1) *A.total = excl + mine64;
+      s_tmp[41] = excl;
+    }
+  }
+  __syncthreads();
+  const uint64_t gbase = s_tmp[41];
+  if (tile_total == 0 || gbase + tile_total > A.cap) return;  // nothing to write / does not fit
+
+  // ---- emit: staged in shared memory when the bucket's pairs fit, else straight to global
+  const bool staged = tile_total <= (uint32_t)BJ_CAP;
+  uint32_t off = t_off;
+#pragma unroll
+  for (int k = 0; k < BJ_ITEMS; ++k) {
+    const uint32_t i = tid + k * BJ_THREADS;
+    if (i < nr && cnt[k]) {
+      const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+      const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
+      for (uint32_t j = b0; j < b1; ++j) {
+        if (!match(rkey[k], rrow[k], j)) continue;
+        if (staged) {
+          s_or[off] = rrow[k];
+          s_os[off] = s_vals[j];
+        } else {
+          A.out_r[gbase + off] = rrow[k];
+          A.out_s[gbase + off] = s_vals[j];
+        }
+        ++off;
+      }
+    }
+  }
+  if (staged) {
+    __syncthreads();
+    for (uint32_t i = tid; i < tile_total; i += BJ_THREADS) {
+      A.out_r[gbase + i] = s_or[i];
+      A.out_s[gbase + i] = s_os[i];
+    }
+  }
+}
+
+}  // namespace
+
+// Whole-operator join through the uniform path: scatter R and S into the same 2^qb buckets, join
+// bucket by bucket.  *ok = 0 when the inputs are not eligible or a bucket overflowed (the host
+// then sorts both relations and merge-joins them); on success the pairs are in the context's
+// result buffers (WS_OUT_R / WS_OUT_S) and *h_num_pairs is their number.
+// kind = HMJ_KEY_U64: r_hash / s_hash are the key columns themselves.  HMJ_KEY_STRING: they are
+// the hash columns and the offsets/chars arrays give the keys for verification.
+int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t nr,
+                         const uint64_t* s_hash, size_t ns, const uint64_t* roff,
+                         const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
+                         cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok) {
+  *ok = 0;
+  if (nr == 0 || ns == 0) return HMJ_OK;
+  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns);
+  if (p.levels == 0) return HMJ_OK;
+  const char* e = getenv("HMJ_JOIN_UNIFORM");
+  if (e && atoi(e) == 0) return HMJ_OK;
+  cudaStream_t st = ctx->stream;
+  hmj_uniform_buckets R, S;
+  HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, nr, 0, p, 0, &R));
+  HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, ns, 0, p, 1, &S));
+  if (ev_partitioned) HMJ_CUDA(ctx, cudaEventRecord(ev_partitioned, st));
+
+  // look-back descriptors + bucket counter + total
+  uint64_t* d_desc = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_JOIN_TILES, (size_t)R.buckets + 4, &d_desc));
+  BJArgs A = {};
+  A.rk = R.keys; A.rv = R.vals; A.rcnt = R.counts; A.rflag = R.flag;
+  A.sk = S.keys; A.sv = S.vals; A.scnt = S.counts; A.sflag = S.flag;
+  A.in_cap = p.cap_seg;
+  A.buckets = R.buckets;
+  A.q = p.qb;
+  A.roff = roff; A.rchars = rchars; A.soff = soff; A.schars = schars;
+  A.desc = d_desc;
+  A.total = d_desc + R.buckets;
+  A.counter = reinterpret_cast<uint32_t*>(d_desc + R.buckets + 1);
+
+  // optimistic capacity: what the buffers already hold, at least max(|R|,|S|) pairs
+  size_t cap = ctx->ws[WS_OUT_R].bytes / 4;
+  const size_t guess = nr > ns ? nr : ns;
+  if (cap < guess) cap = guess;
+  uint32_t *out_r = nullptr, *out_s = nullptr;
+  uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    HMJ_TRY(hmj_ws(ctx, WS_OUT_R, cap, &out_r));
+    HMJ_TRY(hmj_ws(ctx, WS_OUT_S, cap, &out_s));
+    cap = ctx->ws[WS_OUT_R].bytes / 4;
+    if (ctx->ws[WS_OUT_S].bytes / 4 < cap) cap = ctx->ws[WS_OUT_S].bytes / 4;
+    A.out_r = out_r; A.out_s = out_s; A.cap = cap;
+    HMJ_CUDA(ctx, cudaMemsetAsync(d_desc, 0, ((size_t)R.buckets + 4) * 8, st));
+    cudaEvent_t ev;
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_JOIN, ((double)nr + (double)ns) * 12.0, &ev));
+    if (kind == HMJ_KEY_U64) {
+      HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_join_kernel<HMJ_KEY_U64>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM));
+      bucket_join_kernel<HMJ_KEY_U64><<<R.buckets, BJ_THREADS, BJ_SMEM, st>>>(A);
+    } else {
+      HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_join_kernel<HMJ_KEY_STRING>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM));
+      bucket_join_kernel<HMJ_KEY_STRING><<<R.buckets, BJ_THREADS, BJ_SMEM, st>>>(A);
+    }
+    HMJ_LAUNCHED(ctx);
+    hmj_prof_end(ctx, ev);
+    // [0] total pairs, [1] R flag | S flag << 32
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.total, 8, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h + 1), R.flag, 4, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h + 1) + 1, S.flag, 4, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+    if (h[1] != 0) return HMJ_OK;  // overflow: not ok
+    const uint64_t m = h[0];
+    if (m <= cap) {
+      if (ctx->prof_on && ctx->prof_used >= 2) ctx->prof_bytes[ctx->prof_used / 2 - 1] += 8.0 * (double)m;
+      ctx->last_pairs = m;
+      *h_num_pairs = m;
+      *ok = 1;
+      return HMJ_OK;
+    }
+    cap = (size_t)m;  // the buckets are still valid: join again into larger buffers
+  }
+  return hmj_fail(ctx, HMJ_ECAPACITY, "bucket join: result did not fit twice", __FILE__, __LINE__);
+}

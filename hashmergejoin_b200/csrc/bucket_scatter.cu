@@ -376,21 +376,16 @@ int uniform_from_env() {
   return e ? atoi(e) : 1;
 }
 
-struct UniformPlan {
-  int levels = 0;       // 0 = not eligible
-  int bits[2] = {0, 0};
-  int qb = 0;           // total prefix bits = bits[0] + bits[1]
-  uint32_t cap1 = 0;    // slots per level-1 region (two levels only)
-  uint32_t cap_seg = 0; // slots per final bucket
-};
+}  // namespace
 
-// Final buckets of (2048, 4096] pairs on average; one or two scatter levels of <= 8 bits.
-UniformPlan uniform_plan(size_t n) {
-  UniformPlan p;
+// Final buckets of at most 4096 pairs on average for `n_plan` rows (the larger relation of a
+// join, so that both sides share the bucket numbering); one or two scatter levels of <= 8 bits.
+hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan) {
+  hmj_uniform_plan p = {};
   const uint32_t cap_seg = (uint32_t)hmj_segment_sort_cap();
-  if (n <= cap_seg) return p;
+  if (uniform_from_env() == 0 || n_plan <= cap_seg) return p;
   int qb = 0;
-  while (((n + ((size_t)1 << qb) - 1) >> qb) > 4096) ++qb;
+  while (((n_plan + ((size_t)1 << qb) - 1) >> qb) > 4096) ++qb;
   if (qb > 16) return p;
   p.qb = qb;
   p.cap_seg = cap_seg;
@@ -401,45 +396,40 @@ UniformPlan uniform_plan(size_t n) {
     p.levels = 2;
     p.bits[0] = (qb + 1) / 2;
     p.bits[1] = qb - p.bits[0];
-    const double avg1 = (double)n / (double)(1u << p.bits[0]);
-    const double c = avg1 + 8.0 * sqrt(avg1) + 64.0;
-    p.cap1 = ((uint32_t)c + 255u) & ~255u;
   }
   return p;
 }
 
-}  // namespace
-
-// Sorts (keys_in[i], iota_base + i) by (key, row id) with the uniform-hash path.  *ok = 0 when
-// the input is not eligible or a bucket overflowed (nothing usable was written; the input is
-// untouched).  keys_in must not alias keys_out.
-int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
-                         uint64_t* keys_out, uint32_t* vals_out, int* ok) {
-  *ok = 0;
-  if (uniform_from_env() == 0 || keys_in == keys_out) return HMJ_OK;
-  const UniformPlan p = uniform_plan(n);
-  if (p.levels == 0) return HMJ_OK;
+// Scatters (keys_in[i], iota_base + i) into the 2^qb padded buckets of plan `p`.  Bucket b ends
+// up at out->keys/vals[b * cap_seg ...] with out->counts[b] pairs; *out->flag != 0 (device)
+// means a region overflowed and the buckets are void.  `set` selects the workspace slots so
+// that two relations can be held at once (0 or 1).  Nothing is synchronised.
+int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                        const hmj_uniform_plan& p, int set, hmj_uniform_buckets* out) {
   cudaStream_t st = ctx->stream;
   const uint32_t n32 = (uint32_t)n;
   const uint32_t regions1 = 1u << p.bits[0], buckets = 1u << p.qb;
-
+  uint32_t cap1 = 0;
+  if (p.levels == 2) {
+    const double avg1 = (double)n / (double)regions1;
+    cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
+  }
   // scratch words: [flag][level-1 cursors][final cursors][final offsets + 1]
   uint32_t* d_words = nullptr;
   const size_t words = 8 + (size_t)regions1 + buckets + buckets + 1;
-  HMJ_TRY(hmj_ws(ctx, WS_US_CURSORS, words, &d_words));
+  HMJ_TRY(hmj_ws(ctx, set ? WS_US_CURSORS_1 : WS_US_CURSORS, words, &d_words));
   uint32_t* d_flag = d_words;
   uint32_t* d_cur1 = d_words + 8;
   uint32_t* d_cur2 = p.levels == 2 ? d_cur1 + regions1 : d_cur1;
-  uint32_t* d_off = d_cur1 + regions1 + buckets;
   HMJ_CUDA(ctx, cudaMemsetAsync(d_words, 0, (8 + (size_t)regions1 + buckets) * sizeof(uint32_t), st));
 
   uint64_t *d_k1 = nullptr, *d_k2 = nullptr;
   uint32_t *d_v1 = nullptr, *d_v2 = nullptr;
   const size_t slots2 = (size_t)buckets * p.cap_seg;
-  HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_B, slots2, &d_k2));
-  HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_B, slots2, &d_v2));
+  HMJ_TRY(hmj_ws(ctx, set ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, slots2, &d_k2));
+  HMJ_TRY(hmj_ws(ctx, set ? WS_SORT_VALS_C : WS_SORT_VALS_B, slots2, &d_v2));
   if (p.levels == 2) {
-    const size_t slots1 = (size_t)regions1 * p.cap1;
+    const size_t slots1 = (size_t)regions1 * cap1;
     HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, slots1, &d_k1));
     HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, slots1, &d_v1));
   }
@@ -453,41 +443,66 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
   cudaEvent_t ev;
   // level 1: the raw key column -> 2^bits[0] regions
   const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);
-  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
-  if (tma)
-    bucket_scatter_tma_kernel<<<min(tiles, pgrid), UT_THREADS, UT_SMEM, st>>>(
-        keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
-        p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0],
-        p.levels == 2 ? p.cap1 : p.cap_seg, d_cur1, d_flag);
-  else
-    bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
-        keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, p.levels == 2 ? d_k1 : d_k2,
-        p.levels == 2 ? d_v1 : d_v2, 64 - p.bits[0], p.bits[0],
-        p.levels == 2 ? p.cap1 : p.cap_seg, d_cur1, d_flag);
-  HMJ_LAUNCHED(ctx);
-  hmj_prof_end(ctx, ev);
-  if (p.levels == 2) {
-    const uint32_t tpr = (uint32_t)hmj_div_up(p.cap1, US_TILE);
+  uint64_t* k_out1 = p.levels == 2 ? d_k1 : d_k2;
+  uint32_t* v_out1 = p.levels == 2 ? d_v1 : d_v2;
+  const uint32_t cap_out1 = p.levels == 2 ? cap1 : p.cap_seg;
+  if (tiles) {
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
+    if (tma)
+      bucket_scatter_tma_kernel<<<min(tiles, pgrid), UT_THREADS, UT_SMEM, st>>>(
+          keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
+          64 - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
+    else
+      bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
+          keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, k_out1, v_out1, 64 - p.bits[0],
+          p.bits[0], cap_out1, d_cur1, d_flag);
+    HMJ_LAUNCHED(ctx);
+    hmj_prof_end(ctx, ev);
+  }
+  if (p.levels == 2 && tiles) {
+    const uint32_t tpr = (uint32_t)hmj_div_up(cap1, US_TILE);
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
     if (tma)
       bucket_scatter_tma_kernel<<<min(regions1 * tpr, pgrid), UT_THREADS, UT_SMEM, st>>>(
-          d_k1, d_v1, d_cur1, p.cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1],
+          d_k1, d_v1, d_cur1, cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1],
           p.cap_seg, d_cur2, d_flag);
     else
       bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
-          d_k1, d_v1, d_cur1, p.cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg,
+          d_k1, d_v1, d_cur1, cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg,
           d_cur2, d_flag);
     HMJ_LAUNCHED(ctx);
     hmj_prof_end(ctx, ev);
   }
-  bucket_offsets_kernel<<<1, 1024, 0, st>>>(d_cur2, buckets, d_off);
+  out->keys = d_k2;
+  out->vals = d_v2;
+  out->counts = d_cur2;
+  out->offsets = d_cur1 + regions1 + buckets;
+  out->flag = d_flag;
+  out->buckets = buckets;
+  return HMJ_OK;
+}
+
+// Sorts (keys_in[i], iota_base + i) by (key, row id) with the uniform-hash path.  *ok = 0 when
+// the input is not eligible or a bucket overflowed (nothing usable was written; the input is
+// untouched).  keys_in must not alias keys_out.
+int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                         uint64_t* keys_out, uint32_t* vals_out, int* ok) {
+  *ok = 0;
+  if (keys_in == keys_out) return HMJ_OK;
+  const hmj_uniform_plan p = hmj_uniform_plan_for(n);
+  if (p.levels == 0) return HMJ_OK;
+  cudaStream_t st = ctx->stream;
+  hmj_uniform_buckets B;
+  HMJ_TRY(hmj_uniform_scatter(ctx, keys_in, n, iota_base, p, 0, &B));
+  bucket_offsets_kernel<<<1, 1024, 0, st>>>(B.counts, B.buckets, B.offsets);
   HMJ_LAUNCHED(ctx);
+  cudaEvent_t ev;
   HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_FINISH, (double)n * 24.0, &ev));
-  HMJ_TRY(hmj_launch_bucket_finish(ctx, d_k2, d_v2, d_cur2, d_off, buckets, p.cap_seg, p.qb,
-                                   keys_out, vals_out, d_flag));
+  HMJ_TRY(hmj_launch_bucket_finish(ctx, B.keys, B.vals, B.counts, B.offsets, B.buckets, p.cap_seg,
+                                   p.qb, keys_out, vals_out, B.flag));
   hmj_prof_end(ctx, ev);
   uint32_t* h = reinterpret_cast<uint32_t*>(ctx->pinned);
-  HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h, B.flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
   HMJ_CUDA(ctx, cudaStreamSynchronize(st));
   *ok = h[0] == 0;
   return HMJ_OK;

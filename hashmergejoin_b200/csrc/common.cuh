@@ -37,6 +37,9 @@ enum hmj_ws_slot {
   WS_SCALARS,       // small device scalars (counters, sums)
   WS_SEG_WINDOWS,   // window table of the segment sort
   WS_US_CURSORS,    // uniform sort: flag, bucket cursors, dense offsets
+  WS_US_CURSORS_1,  // ... of the second relation (bucket join)
+  WS_SORT_KEYS_C,   // padded buckets of the second relation (bucket join)
+  WS_SORT_VALS_C,
   WS_HASH_TMP0,     // unsorted hash columns (strings), so that the sort never runs in place
   WS_HASH_TMP1,
   WS_NUM_SLOTS
@@ -160,6 +163,28 @@ int hmj_launch_bucket_finish(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, const
                              const uint32_t* offsets, uint32_t buckets, uint32_t in_cap, int q,
                              uint64_t* out_keys, uint32_t* out_vals, uint32_t* d_flag);
 // bucket_scatter.cu
+struct hmj_uniform_plan {
+  int levels;        // 0 = not eligible
+  int bits[2];
+  int qb;            // total prefix bits = bits[0] + bits[1]
+  uint32_t cap_seg;  // slots per final bucket
+};
+struct hmj_uniform_buckets {
+  uint64_t* keys;     // bucket b at [b * cap_seg ...)
+  uint32_t* vals;
+  uint32_t* counts;   // [buckets]
+  uint32_t* offsets;  // [buckets + 1] scratch for the dense offsets
+  uint32_t* flag;     // != 0: a region overflowed
+  uint32_t buckets;
+};
+hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan);
+int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                        const hmj_uniform_plan& p, int set, hmj_uniform_buckets* out);
+// bucket_join.cu
+int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t nr,
+                         const uint64_t* s_hash, size_t ns, const uint64_t* roff,
+                         const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
+                         cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok);
 int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                          uint64_t* keys_out, uint32_t* vals_out, int* ok);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,

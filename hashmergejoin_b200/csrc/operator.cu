@@ -34,6 +34,17 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   ctx->tm.sort_uniform = 0;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));  // identity hash: no kernel
+  {
+    // uniform hashes: partition both sides on the same hash bits, join bucket by bucket
+    int ok = 0;
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_U64, d_rkeys, nr, d_skeys, ns, nullptr, nullptr,
+                                 nullptr, nullptr, ctx->ev[EV_SORTED], h_num_pairs, &ok));
+    if (ok) {
+      ctx->tm.sort_uniform += 2;
+      HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+      return HMJ_OK;
+    }
+  }
   hmj_relation R = {}, S = {};
   uint64_t* h = nullptr;
   uint32_t* rid = nullptr;
@@ -71,6 +82,16 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   HMJ_TRY(hmj_hash_strings(ctx, d_roffsets, d_rchars, nr, rt));
   HMJ_TRY(hmj_hash_strings(ctx, d_soffsets, d_schars, ns, st));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
+  {
+    int ok = 0;
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nr, st, ns, d_roffsets, d_rchars,
+                                 d_soffsets, d_schars, ctx->ev[EV_SORTED], h_num_pairs, &ok));
+    if (ok) {
+      ctx->tm.sort_uniform += 2;
+      HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+      return HMJ_OK;
+    }
+  }
   HMJ_TRY(hmj_sort_pairs(ctx, rt, nullptr, nr, rh, rr));
   HMJ_TRY(hmj_sort_pairs(ctx, st, nullptr, ns, sh, sr));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
