@@ -259,7 +259,7 @@ def run_gpu(args):
     # are accumulated by the library at the launch sites.
     peak, peak_src = peaks()
     names = ["onesweep_pass_kernel", "bucket_scatter_tma_kernel", "segment_sort_kernel",
-             "join_tile_kernel", "radix_histogram_kernel", "hash_strings_kernel"]
+             "join_tile_kernel", "radix_histogram_kernel", "hash_strings_kernel", "bucket_join_kernel"]
     kernels = {}
     for i, nm in enumerate(names):
         ln, ms_sum, by = tm["kernel_launches"][i], tm["kernel_ms"][i], tm["kernel_bytes"][i]

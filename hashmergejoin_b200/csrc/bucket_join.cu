@@ -9,10 +9,10 @@
 // compares the full 64-bit hashes (and, for strings, the keys: hashjoin.h:139-141) and emits
 // (build_row, probe_row).  That removes the write of both sorted relations (12 B per tuple), their
 // re-read by the merge join (12 B per tuple) and the merge-path search.
-// Output: pairs of bucket b come before those of bucket b+1 (ascending hash prefix; offsets from
-// a decoupled look-back over per-bucket totals, as merge_join.cu), staged in shared memory and
-// written with coalesced stores.  Inside a bucket the order follows the arrival order of the
-// scatter and is not specified (the reference leaves the order of equal hashes unspecified too).
+// Output: a bucket's pairs are staged in shared memory and written with coalesced stores at a
+// position reserved with one atomicAdd on the global pair counter.  The ORDER of the pairs is
+// therefore unspecified (bucket arrival order; inside a bucket the arrival order of the
+// scatter); hmj_merge_join_write on sorted relations gives hash order when that is wanted.
 // Algorithmic bytes: 12 per input tuple + 8 per output pair.
 #include "common.cuh"
 #include "join_device.cuh"
@@ -24,12 +24,8 @@ constexpr int BJ_ITEMS = 9;
 constexpr int BJ_CAP = BJ_THREADS * BJ_ITEMS;  // == hmj_segment_sort_cap()
 constexpr int BJ_BINS = 4096;
 constexpr int BJ_PER = BJ_BINS / BJ_THREADS;
-constexpr size_t BJ_SMEM = (size_t)BJ_CAP * 8 + (size_t)BJ_CAP * 4 + (size_t)(BJ_BINS + 1) * 4 +
-                           2 * (size_t)BJ_CAP * 4 + 64 * 8 + 64;
-
-constexpr uint64_t BD_PARTIAL = 1ull << 62;
-constexpr uint64_t BD_INCLUSIVE = 2ull << 62;
-constexpr uint64_t BD_VALUE = (1ull << 62) - 1;
+constexpr size_t BJ_SMEM = (size_t)BJ_CAP * 8 + (size_t)BJ_CAP * 8 + (size_t)BJ_CAP * 4 +
+                           (size_t)(BJ_BINS + 1) * 4 + 64 * 8 + 64;
 
 struct BJArgs {
   const uint64_t* rk; const uint32_t* rv; const uint32_t* rcnt; const uint32_t* rflag;
@@ -40,60 +36,63 @@ struct BJArgs {
   const uint64_t* soff; const uint8_t* schars;
   uint32_t* out_r; uint32_t* out_s;
   uint64_t cap;            // capacity of out_r / out_s in pairs
-  uint64_t* desc;          // [buckets] look-back descriptors (zeroed)
-  uint32_t* counter;       // dynamic bucket ids (zeroed)
-  uint64_t* total;         // number of pairs of the whole join
+  uint64_t* total;         // number of pairs of the whole join (zeroed; output cursor)
 };
 
-__device__ __forceinline__ void bd_store(uint64_t* p, uint64_t v) {
-  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ uint64_t bd_load(const uint64_t* p) {
-  uint64_t v;
-  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
+__device__ __forceinline__ uint32_t bj_smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
 }
 
 template <int KIND>
 __global__ void __launch_bounds__(BJ_THREADS, 2)
 bucket_join_kernel(const BJArgs A) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);   // S hashes, grouped by bin
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  // R hashes arrive here by a bulk async copy; once every thread holds its R pairs in registers
+  // the same bytes stage the output pairs (s_or / s_os)
+  uint64_t* s_rk = reinterpret_cast<uint64_t*>(smem_raw);
+  uint32_t* s_or = reinterpret_cast<uint32_t*>(smem_raw);
+  uint32_t* s_os = s_or + BJ_CAP;
+  uint64_t* s_keys = s_rk + BJ_CAP;                           // S hashes, grouped by bin
   uint32_t* s_vals = reinterpret_cast<uint32_t*>(s_keys + BJ_CAP);
   uint32_t* s_bin = s_vals + BJ_CAP;                          // [BINS + 1]
-  uint32_t* s_or = s_bin + BJ_BINS + 1;                       // staged output pairs
-  uint32_t* s_os = s_or + BJ_CAP;
   uint64_t* s_tmp = reinterpret_cast<uint64_t*>(
-      (reinterpret_cast<uintptr_t>(s_os + BJ_CAP) + 7) & ~uintptr_t(7));  // [64]
+      (reinterpret_cast<uintptr_t>(s_bin + BJ_BINS + 1) + 7) & ~uintptr_t(7));  // [64]
+  uint64_t* s_bar = s_tmp + 48;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t b = blockIdx.x;
 
-  if (tid == 0) s_tmp[40] = atomicAdd(A.counter, 1u);
-  __syncthreads();
-  const uint32_t b = (uint32_t)s_tmp[40];
   // a scatter level overflowed somewhere: the buckets are void, the host takes the other path
   const bool dead = *reinterpret_cast<const volatile uint32_t*>(A.rflag) != 0 ||
                     *reinterpret_cast<const volatile uint32_t*>(A.sflag) != 0;
   if (dead) return;
   const uint32_t nr = min(A.rcnt[b], A.in_cap), ns = min(A.scnt[b], A.in_cap);
+  if (nr == 0 || ns == 0) return;
   const uint32_t base_slot = b * A.in_cap;
 
-  // ---- both buckets into registers
-  uint64_t rkey[BJ_ITEMS], skey[BJ_ITEMS];
-  uint32_t rrow[BJ_ITEMS], srow[BJ_ITEMS];
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bj_smem_u32(s_bar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // (the copy length is rounded up to 16 bytes: the extra slot lies inside the bucket's region)
+    const uint32_t bytes = ((nr + 1u) & ~1u) * 8u;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bj_smem_u32(s_bar)),
+                 "r"(bytes)
+                 : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(bj_smem_u32(s_rk)),
+        "l"(A.rk + base_slot), "r"(bytes), "r"(bj_smem_u32(s_bar))
+        : "memory");
+  }
+
+  // ---- S bucket into registers
+  uint64_t skey[BJ_ITEMS];
+  uint32_t srow[BJ_ITEMS];
 #pragma unroll
   for (int k = 0; k < BJ_ITEMS; ++k) {
     const uint32_t i = tid + k * BJ_THREADS;
     if (i < ns) {
       skey[k] = A.sk[base_slot + i];
       srow[k] = A.sv[base_slot + i];
-    }
-  }
-#pragma unroll
-  for (int k = 0; k < BJ_ITEMS; ++k) {
-    const uint32_t i = tid + k * BJ_THREADS;
-    if (i < nr) {
-      rkey[k] = A.rk[base_slot + i];
-      rrow[k] = A.rv[base_slot + i];
     }
   }
   for (int i = tid; i <= BJ_BINS; i += BJ_THREADS) s_bin[i] = 0;
@@ -103,74 +102,124 @@ bucket_join_kernel(const BJArgs A) {
   __syncthreads();
 
   // ---- S: counting sort on the 12 bits below the prefix
-  uint16_t slot[BJ_ITEMS];
-#pragma unroll
-  for (int k = 0; k < BJ_ITEMS; ++k) {
-    const uint32_t i = tid + k * BJ_THREADS;
-    if (i < ns) slot[k] = (uint16_t)atomicAdd(&s_bin[(uint32_t)((skey[k] - kbase) >> s)], 1u);
-  }
-  __syncthreads();
   {
-    uint32_t c[BJ_PER], sum = 0;
+    uint16_t slot[BJ_ITEMS];
 #pragma unroll
-    for (int j = 0; j < BJ_PER; ++j) {
-      c[j] = s_bin[tid * BJ_PER + j];
-      sum += c[j];
+    for (int k = 0; k < BJ_ITEMS; ++k) {
+      const uint32_t i = tid + k * BJ_THREADS;
+      if (i < ns) slot[k] = (uint16_t)atomicAdd(&s_bin[(uint32_t)((skey[k] - kbase) >> s)], 1u);
     }
-    uint32_t x = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    uint32_t* s_w = reinterpret_cast<uint32_t*>(s_tmp);
-    if (lane == 31) s_w[warp] = x;
     __syncthreads();
-    uint32_t wt = lane < warp ? s_w[lane] : 0;  // 16 warps
+    {
+      uint32_t c[BJ_PER], sum = 0;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
-    uint32_t pre = wt + x - sum;
+      for (int j = 0; j < BJ_PER; ++j) {
+        c[j] = s_bin[tid * BJ_PER + j];
+        sum += c[j];
+      }
+      uint32_t x = sum;
 #pragma unroll
-    for (int j = 0; j < BJ_PER; ++j) {
-      s_bin[tid * BJ_PER + j] = pre;
-      pre += c[j];
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+        if (lane >= o) x += y;
+      }
+      uint32_t* s_w = reinterpret_cast<uint32_t*>(s_tmp);
+      if (lane == 31) s_w[warp] = x;
+      __syncthreads();
+      uint32_t wt = lane < warp ? s_w[lane] : 0;  // 16 warps
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
+      uint32_t pre = wt + x - sum;
+#pragma unroll
+      for (int j = 0; j < BJ_PER; ++j) {
+        s_bin[tid * BJ_PER + j] = pre;
+        pre += c[j];
+      }
+      if (tid == 0) s_bin[BJ_BINS] = ns;
     }
-    if (tid == 0) s_bin[BJ_BINS] = ns;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < BJ_ITEMS; ++k) {
+      const uint32_t i = tid + k * BJ_THREADS;
+      if (i < ns) {
+        const uint32_t p = s_bin[(uint32_t)((skey[k] - kbase) >> s)] + slot[k];
+        s_keys[p] = skey[k];
+        s_vals[p] = srow[k];
+      }
+    }
   }
-  __syncthreads();
+
+  // ---- R pairs: hashes from the bulk copy, row ids straight from global memory (they are not
+  // needed before the emit, so their latency hides behind the probe)
+  {
+    const uint32_t sbar = bj_smem_u32(s_bar);
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t"
+        "}" ::"r"(sbar)
+        : "memory");
+  }
+  uint64_t rkey[BJ_ITEMS];
+  uint32_t rrow[BJ_ITEMS];
 #pragma unroll
   for (int k = 0; k < BJ_ITEMS; ++k) {
     const uint32_t i = tid + k * BJ_THREADS;
-    if (i < ns) {
-      const uint32_t p = s_bin[(uint32_t)((skey[k] - kbase) >> s)] + slot[k];
-      s_keys[p] = skey[k];
-      s_vals[p] = srow[k];
+    if (i < nr) {
+      rkey[k] = s_rk[i];
+      rrow[k] = A.rv[base_slot + i];
     }
   }
-  __syncthreads();
+  __syncthreads();  // S is grouped; every thread has taken its R hashes out of the staging bytes
 
-  // ---- R probes: matches of every R pair among the S pairs of its bin
+  // ---- probe: matches of every R pair among the S pairs of its bin.  cnt = number of matches,
+  // hit = slot of the first one (the only one unless S holds duplicates of the key).
   auto match = [&](uint64_t key, uint32_t row, uint32_t j) -> bool {
     if (s_keys[j] != key) return false;
     if (KIND == HMJ_KEY_U64) return true;
     return keys_equal_str(A.roff, A.rchars, row, A.soff, A.schars, s_vals[j]);
   };
   uint32_t mine = 0;
-  uint16_t cnt[BJ_ITEMS];
+  uint16_t cnt[BJ_ITEMS], hit[BJ_ITEMS];
 #pragma unroll
   for (int k = 0; k < BJ_ITEMS; ++k) {
     const uint32_t i = tid + k * BJ_THREADS;
     cnt[k] = 0;
+    hit[k] = 0;
     if (i < nr) {
       const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
-      const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
-      uint32_t c = 0;
-      for (uint32_t j = b0; j < b1; ++j) c += match(rkey[k], rrow[k], j) ? 1u : 0u;
+      const uint32_t b0 = s_bin[d], n = s_bin[d + 1] - b0;
+      uint32_t c = 0, first = 0;
+      if (KIND == HMJ_KEY_U64) {
+        // four slots at once without a branch (reads past the bin are masked), then the rest
+#pragma unroll
+        for (uint32_t j = 0; j < 4; ++j) {
+          const bool m = j < n && s_keys[min(b0 + j, (uint32_t)BJ_CAP - 1)] == rkey[k];
+          if (m && c == 0) first = b0 + j;
+          c += m ? 1u : 0u;
+        }
+        for (uint32_t j = 4; j < n; ++j) {
+          const bool m = s_keys[b0 + j] == rkey[k];
+          if (m && c == 0) first = b0 + j;
+          c += m ? 1u : 0u;
+        }
+      } else {
+        for (uint32_t j = 0; j < n; ++j) {
+          const bool m = match(rkey[k], rrow[k], b0 + j);
+          if (m && c == 0) first = b0 + j;
+          c += m ? 1u : 0u;
+        }
+      }
       cnt[k] = (uint16_t)c;  // a bin holds <= CAP pairs
+      hit[k] = (uint16_t)first;
       mine += c;
     }
   }
-  // exclusive scan of the per-thread totals (thread-major order of the output)
+  // exclusive scan of the per-thread totals
   uint32_t t_off, tile_total;
   {
     uint32_t x = mine;
@@ -180,79 +229,71 @@ bucket_join_kernel(const BJArgs A) {
       if (lane >= o) x += y;
     }
     uint32_t* s_w = reinterpret_cast<uint32_t*>(s_tmp);
-    __syncthreads();
-    if (lane == 31) s_w[warp] = x;
+    if (lane == 31) s_w[32 + warp] = x;
     __syncthreads();
     uint32_t wt = 0, tot = 0;
 #pragma unroll
     for (int w = 0; w < BJ_THREADS / 32; ++w) {
-      const uint32_t t = s_w[w];
+      const uint32_t t = s_w[32 + w];
       if (w < warp) wt += t;
       tot += t;
     }
     t_off = wt + x - mine;
     tile_total = tot;
   }
-
-  // ---- global offset of the bucket: decoupled look-back, one warp, 32 descriptors per trip
-  if (warp == 0) {
-    const uint64_t mine64 = tile_total;
-    if (lane == 0 && b != 0) bd_store(A.desc + b, BD_PARTIAL | mine64);
-    uint64_t excl = 0;
-    int64_t first_idx = (int64_t)b - 1;
-    while (first_idx >= 0) {
-      const int64_t idx = first_idx - lane;
-      uint64_t d = BD_INCLUSIVE;  // before bucket 0: an inclusive prefix of zero
-      if (idx >= 0) {
-        d = bd_load(A.desc + idx);
-        while ((d >> 62) == 0) d = bd_load(A.desc + idx);
-      }
-      const uint32_t incl = __ballot_sync(0xffffffffu, (d >> 62) == 2);
-      const int stop = incl ? (__ffs(incl) - 1) : 31;
-      uint64_t c = (lane <= stop) ? (d & BD_VALUE) : 0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-      excl += c;
-      if (incl) break;
-      first_idx -= 32;
-    }
-    if (lane == 0) {
-      bd_store(A.desc + b, BD_INCLUSIVE | (excl + mine64));
-      if (b == A.buckets - 1) *A.total = excl + mine64;
-      s_tmp[41] = excl;
-    }
-  }
-  __syncthreads();
-  const uint64_t gbase = s_tmp[41];
-  if (tile_total == 0 || gbase + tile_total > A.cap) return;  // nothing to write / does not fit
+  if (tile_total == 0) return;
+  // ---- room for the bucket's pairs: one atomicAdd on the global pair counter (buckets land in
+  // the output in the order in which they get here)
+  if (tid == 0) s_tmp[40] = atomicAdd(reinterpret_cast<unsigned long long*>(A.total),
+                                      (unsigned long long)tile_total);
 
   // ---- emit: staged in shared memory when the bucket's pairs fit, else straight to global
   const bool staged = tile_total <= (uint32_t)BJ_CAP;
-  uint32_t off = t_off;
+  if (staged) {
+    uint32_t off = t_off;
 #pragma unroll
-  for (int k = 0; k < BJ_ITEMS; ++k) {
-    const uint32_t i = tid + k * BJ_THREADS;
-    if (i < nr && cnt[k]) {
-      const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
-      const uint32_t b0 = s_bin[d], b1 = s_bin[d + 1];
-      for (uint32_t j = b0; j < b1; ++j) {
-        if (!match(rkey[k], rrow[k], j)) continue;
-        if (staged) {
-          s_or[off] = rrow[k];
-          s_os[off] = s_vals[j];
-        } else {
-          A.out_r[gbase + off] = rrow[k];
-          A.out_s[gbase + off] = s_vals[j];
-        }
+    for (int k = 0; k < BJ_ITEMS; ++k) {
+      const uint32_t i = tid + k * BJ_THREADS;
+      if (i < nr && cnt[k]) {
+        s_or[off] = rrow[k];
+        s_os[off] = s_vals[hit[k]];
         ++off;
+        if (cnt[k] > 1) {
+          const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+          const uint32_t b1 = s_bin[d + 1];
+          for (uint32_t j = (uint32_t)hit[k] + 1; j < b1; ++j) {
+            if (!match(rkey[k], rrow[k], j)) continue;
+            s_or[off] = rrow[k];
+            s_os[off] = s_vals[j];
+            ++off;
+          }
+        }
       }
     }
   }
+  __syncthreads();
+  const uint64_t gbase = s_tmp[40];
+  if (gbase + tile_total > A.cap) return;  // does not fit: the host re-runs with the exact size
   if (staged) {
-    __syncthreads();
     for (uint32_t i = tid; i < tile_total; i += BJ_THREADS) {
       A.out_r[gbase + i] = s_or[i];
       A.out_s[gbase + i] = s_os[i];
+    }
+  } else {
+    uint64_t off = gbase + t_off;
+#pragma unroll
+    for (int k = 0; k < BJ_ITEMS; ++k) {
+      const uint32_t i = tid + k * BJ_THREADS;
+      if (i < nr && cnt[k]) {
+        const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+        const uint32_t b1 = s_bin[d + 1];
+        for (uint32_t j = hit[k]; j < b1; ++j) {
+          if (!match(rkey[k], rrow[k], j)) continue;
+          A.out_r[off] = rrow[k];
+          A.out_s[off] = s_vals[j];
+          ++off;
+        }
+      }
     }
   }
 }
@@ -281,9 +322,9 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t 
   HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, ns, 0, p, 1, &S));
   if (ev_partitioned) HMJ_CUDA(ctx, cudaEventRecord(ev_partitioned, st));
 
-  // look-back descriptors + bucket counter + total
+  // the global pair counter
   uint64_t* d_desc = nullptr;
-  HMJ_TRY(hmj_ws(ctx, WS_JOIN_TILES, (size_t)R.buckets + 4, &d_desc));
+  HMJ_TRY(hmj_ws(ctx, WS_JOIN_TILES, 4, &d_desc));
   BJArgs A = {};
   A.rk = R.keys; A.rv = R.vals; A.rcnt = R.counts; A.rflag = R.flag;
   A.sk = S.keys; A.sv = S.vals; A.scnt = S.counts; A.sflag = S.flag;
@@ -291,9 +332,7 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t 
   A.buckets = R.buckets;
   A.q = p.qb;
   A.roff = roff; A.rchars = rchars; A.soff = soff; A.schars = schars;
-  A.desc = d_desc;
-  A.total = d_desc + R.buckets;
-  A.counter = reinterpret_cast<uint32_t*>(d_desc + R.buckets + 1);
+  A.total = d_desc;
 
   // optimistic capacity: what the buffers already hold, at least max(|R|,|S|) pairs
   size_t cap = ctx->ws[WS_OUT_R].bytes / 4;
@@ -307,9 +346,9 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t 
     cap = ctx->ws[WS_OUT_R].bytes / 4;
     if (ctx->ws[WS_OUT_S].bytes / 4 < cap) cap = ctx->ws[WS_OUT_S].bytes / 4;
     A.out_r = out_r; A.out_s = out_s; A.cap = cap;
-    HMJ_CUDA(ctx, cudaMemsetAsync(d_desc, 0, ((size_t)R.buckets + 4) * 8, st));
+    HMJ_CUDA(ctx, cudaMemsetAsync(d_desc, 0, 32, st));
     cudaEvent_t ev;
-    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_JOIN, ((double)nr + (double)ns) * 12.0, &ev));
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_BJOIN, ((double)nr + (double)ns) * 12.0, &ev));
     if (kind == HMJ_KEY_U64) {
       HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_join_kernel<HMJ_KEY_U64>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BJ_SMEM));

@@ -203,7 +203,8 @@ enum hmj_kernel_class {
   HMJ_K_FINISH = 2,  /* segment_sort_kernel / bucket_finish_kernel */
   HMJ_K_JOIN = 3,    /* join_tile_kernel */
   HMJ_K_HIST = 4,    /* radix_histogram_kernel */
-  HMJ_K_HASH = 5     /* hash_strings_kernel */
+  HMJ_K_HASH = 5,    /* hash_strings_kernel */
+  HMJ_K_BJOIN = 6    /* bucket_join_kernel (uniform-hash whole-operator path) */
 };
 int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
 /* on != 0: bracket every onesweep-pass launch with CUDA events on the context's stream and
