@@ -144,12 +144,13 @@ bucket_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
 // in flight and no thread holds registers for them (the plain kernel above exposes the row-id
 // load latency: profiles/r1d, 54 % of its stall samples).  The tile is permuted in place in its
 // buffer and leaves with coalesced stores.
-constexpr int UT_THREADS = 512;
 constexpr int UT_ITEMS = 8;
-constexpr int UT_TILE = UT_THREADS * UT_ITEMS;  // 4096, must equal US_TILE (same tile grid)
-static_assert(UT_TILE == US_TILE, "tile grids must agree");
-constexpr size_t UT_BUF_BYTES = (size_t)UT_TILE * 12;
-constexpr size_t UT_SMEM = 2 * UT_BUF_BYTES + 3 * US_MAX_BINS * 4 + 32 * 4 + 64;
+template <int THREADS>
+struct UtCfg {
+  static constexpr int TILE = THREADS * UT_ITEMS;
+  static constexpr size_t BUF_BYTES = (size_t)TILE * 12;
+  static constexpr size_t SMEM = 2 * BUF_BYTES + 4 * US_MAX_BINS * 4 + 32 * 4 + 64;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
@@ -184,18 +185,22 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
       : "memory");
 }
 
-__global__ void __launch_bounds__(UT_THREADS, 2)
+template <int UT_THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
 bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           const uint32_t* __restrict__ in_counts, uint32_t in_stride,
                           uint32_t n_single, uint32_t tiles_per_region, uint32_t total_tiles,
                           uint32_t iota_base, uint64_t* __restrict__ keys_out,
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
                           uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag) {
+  constexpr int UT_TILE = UtCfg<UT_THREADS>::TILE;
+  constexpr size_t UT_BUF_BYTES = UtCfg<UT_THREADS>::BUF_BYTES;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + 2 * UT_BUF_BYTES);
   uint32_t* s_off = s_cnt + US_MAX_BINS;
   uint32_t* s_gbase = s_off + US_MAX_BINS;
-  uint32_t* s_scan = s_gbase + US_MAX_BINS;  // [32]
+  uint32_t* s_rcount = s_gbase + US_MAX_BINS;  // [regions <= 256] pairs per input region
+  uint32_t* s_scan = s_rcount + US_MAX_BINS;   // [32]
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_scan + 32);  // [2]
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -206,12 +211,17 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     mbar_init(&s_bar[1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
+  if (in_counts) {
+    const uint32_t regions = (total_tiles + tiles_per_region - 1) / tiles_per_region;
+    for (uint32_t r = tid; r < regions; r += UT_THREADS)
+      s_rcount[r] = min(in_counts[r * US_CURSOR_STRIDE], in_stride);
+  }
   __syncthreads();
 
   // tile t -> (region, first pair, number of pairs); 0 pairs = nothing there
   auto tile_of = [&](uint32_t t, uint32_t* in_base) -> uint32_t {
     const uint32_t r = t / tiles_per_region, j = t % tiles_per_region;
-    const uint32_t count = in_counts ? min(in_counts[r * US_CURSOR_STRIDE], in_stride) : n_single;
+    const uint32_t count = in_counts ? s_rcount[r] : n_single;
     const uint64_t first = (uint64_t)j * UT_TILE;
     if (first >= count) return 0;
     *in_base = r * in_stride + (uint32_t)first;
@@ -435,23 +445,37 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_
   }
   HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
-  HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)UT_SMEM));
   // bulk copies need 16-byte aligned sources (tile starts are multiples of 4096 pairs)
   const bool tma = uniform_from_env() != 2 && (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0;
-  const uint32_t pgrid = (uint32_t)ctx->num_sms * 2;
+  const char* ecfg = getenv("HMJ_SCATTER_CFG");
+  const int scfg = ecfg ? atoi(ecfg) : 0;
   cudaEvent_t ev;
   // level 1: the raw key column -> 2^bits[0] regions
-  const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);
+  const uint32_t tile_items = !tma ? US_TILE : scfg == 1 ? 2048 : scfg == 2 ? 3072 : scfg == 3 ? 8192 : 4096;
+  const uint32_t tiles = (uint32_t)hmj_div_up(n, tile_items);
+#define HMJ_TMA_LAUNCH(T, B, NT, ...)                                                              \
+  do {                                                                                            \
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<T, B>,                           \
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,               \
+                                       (int)UtCfg<T>::SMEM));                                     \
+    bucket_scatter_tma_kernel<T, B><<<min((uint32_t)(NT), (uint32_t)ctx->num_sms * B), T,         \
+                                      UtCfg<T>::SMEM, st>>>(__VA_ARGS__);                         \
+  } while (0)
+#define HMJ_TMA_DISPATCH(NT, ...)                                     \
+  do {                                                               \
+    if (scfg == 1) HMJ_TMA_LAUNCH(256, 4, NT, __VA_ARGS__);           \
+    else if (scfg == 2) HMJ_TMA_LAUNCH(384, 3, NT, __VA_ARGS__);      \
+    else if (scfg == 3) HMJ_TMA_LAUNCH(1024, 1, NT, __VA_ARGS__);     \
+    else HMJ_TMA_LAUNCH(512, 2, NT, __VA_ARGS__);                     \
+  } while (0)
   uint64_t* k_out1 = p.levels == 2 ? d_k1 : d_k2;
   uint32_t* v_out1 = p.levels == 2 ? d_v1 : d_v2;
   const uint32_t cap_out1 = p.levels == 2 ? cap1 : p.cap_seg;
   if (tiles) {
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
     if (tma)
-      bucket_scatter_tma_kernel<<<min(tiles, pgrid), UT_THREADS, UT_SMEM, st>>>(
-          keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
-          64 - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
+      HMJ_TMA_DISPATCH(tiles, keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
+                       64 - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
     else
       bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
           keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, k_out1, v_out1, 64 - p.bits[0],
@@ -460,12 +484,11 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_
     hmj_prof_end(ctx, ev);
   }
   if (p.levels == 2 && tiles) {
-    const uint32_t tpr = (uint32_t)hmj_div_up(cap1, US_TILE);
+    const uint32_t tpr = (uint32_t)hmj_div_up(cap1, tile_items);
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
     if (tma)
-      bucket_scatter_tma_kernel<<<min(regions1 * tpr, pgrid), UT_THREADS, UT_SMEM, st>>>(
-          d_k1, d_v1, d_cur1, cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1],
-          p.cap_seg, d_cur2, d_flag);
+      HMJ_TMA_DISPATCH(regions1 * tpr, d_k1, d_v1, d_cur1, cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2,
+                       64 - p.qb, p.bits[1], p.cap_seg, d_cur2, d_flag);
     else
       bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
           d_k1, d_v1, d_cur1, cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg,

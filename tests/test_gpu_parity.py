@@ -292,6 +292,61 @@ def test_join_unique_u64(ctx, oracle):
     assert out_r.size == 100000
 
 
+def check_operator_u64(ctx, oracle, rk, sk):
+    """the whole operator (hmj_join_u64: HashMergeJoin ctor + full iteration) against the oracle"""
+    rk, sk = np.ascontiguousarray(rk, np.uint64), np.ascontiguousarray(sk, np.uint64)
+    m = ctx.join_u64(dev(rk), dev(sk))
+    out_r, out_s = ctx.join_result_to_host(m)
+    t_r, t_s, _ = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert m == t_r.size and np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+    return m
+
+
+def test_operator_bucket_join_path(ctx, oracle):
+    # uniform hashes: the whole-operator join takes the bucket path (bucket_join.cu)
+    rng = np.random.default_rng(41)
+    n = 900000
+    keys = datagen.unique_u64(n, seed=5)
+    rk, sk = datagen.permuted(keys, 1).copy(), datagen.permuted(keys, 2).copy()
+    u0 = ctx.timings()["sort_uniform"]
+    assert check_operator_u64(ctx, oracle, rk, sk) == n
+    assert ctx.timings()["sort_uniform"] == 2, "the bucket join did not run"
+    # 300 x 300 copies of one key: 90000 pairs from one bucket (more than its staging area)
+    rk[rng.choice(n, 300, replace=False)] = np.uint64(0x9E3779B97F4A7C15)
+    sk[rng.choice(n, 300, replace=False)] = np.uint64(0x9E3779B97F4A7C15)
+    assert check_operator_u64(ctx, oracle, rk, sk) >= 90000
+    assert ctx.timings()["sort_uniform"] == 2
+    # different sizes on the two sides share the bucket numbering of the larger one
+    check_operator_u64(ctx, oracle, rk[:50000], sk)
+    check_operator_u64(ctx, oracle, rk, sk[:7000])
+    # every key twice on one side, four times on the other, plus non-matching rows
+    base = datagen.unique_u64(120000, seed=6)
+    rk2 = np.concatenate([base[:100000], base[:100000]])[rng.permutation(200000)]
+    sk2 = np.concatenate([base[20000:]] * 4)[rng.permutation(400000)]
+    check_operator_u64(ctx, oracle, rk2, sk2)
+
+
+@pytest.mark.parametrize("nr,ns,rng_hi", [(0, 10, 5), (10, 0, 5), (1, 3, 1), (5000, 7000, 600),
+                                          (30000, 100, 50), (20000, 20000, 2 ** 63), (4609, 4609, 2 ** 64)])
+def test_operator_shapes_fall_back_or_not(ctx, oracle, nr, ns, rng_hi):
+    rng = np.random.default_rng(nr * 11 + ns)
+    check_operator_u64(ctx, oracle, rng.integers(0, rng_hi, size=nr, dtype=np.uint64),
+                       rng.integers(0, rng_hi, size=ns, dtype=np.uint64))
+
+
+def test_operator_strings_bucket_join(ctx, oracle):
+    off, chars, _, _ = datagen.strgen(50000, seed=7, shuffle_seed=1)
+    rng = np.random.default_rng(4)
+    roff, rchars = datagen.take_rows(off, chars, rng.integers(0, 50000, size=60000))
+    soff, schars = datagen.take_rows(off, chars, rng.integers(0, 50000, size=40000))
+    out_r, out_s = gpu_join_strings(ctx, roff, rchars, soff, schars)
+    assert ctx.timings()["sort_uniform"] == 2, "the bucket join did not run"
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars))
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+
+
 def test_join_golden_duplicates(ctx, oracle):
     g = G.load("dup_join_u64.json")
     rk, sk = G.u64(g["r_keys"]), G.u64(g["s_keys"])
