@@ -73,6 +73,7 @@ SIGNATURES = {
     "hmj_merge_join_write": (_I, [_P, _RELP, _RELP, _P, _P, _SZ, _U64P]),
     "hmj_merge_join_aggregate": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),
     "hmj_join_u64": (_I, [_P, _P, _SZ, _P, _SZ, _U64P]),
+    "hmj_join_pairs": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _I, _U64P]),
     "hmj_join_strings": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
     "hmj_join_result": (_I, [_P, C.POINTER(_P), C.POINTER(_P), _U64P]),
     "hmj_join_result_to_host": (_I, [_P, _P, _P, _SZ]),

@@ -164,6 +164,20 @@ class Context:
                                        skeys.numel(), C.byref(m)))
         return m.value
 
+    def join_pairs(self, rhash, rrowid, shash, srowid, prefix_bits=0):
+        """hmj_join_pairs: unsorted (hash, row id) relations of one hash range (multi-GPU local step)"""
+        m = C.c_uint64()
+        self._ck(self.lib.hmj_join_pairs(self.h, _dptr(rhash), _dptr(rrowid), rhash.numel(),
+                                         _dptr(shash), _dptr(srowid), shash.numel(), prefix_bits,
+                                         C.byref(m)))
+        return m.value
+
+    def join_result(self):
+        """device views (int32 tensors) of the last whole-operator result"""
+        pr, ps, m = C.c_void_p(), C.c_void_p(), C.c_uint64()
+        self._ck(self.lib.hmj_join_result(self.h, C.byref(pr), C.byref(ps), C.byref(m)))
+        return pr.value, ps.value, m.value
+
     def join_strings(self, roff, rchars, soff, schars):
         m = C.c_uint64()
         self._ck(self.lib.hmj_join_strings(self.h, _dptr(roff), _dptr(rchars), roff.numel() - 1,

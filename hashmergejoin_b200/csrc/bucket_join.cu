@@ -31,7 +31,7 @@ struct BJArgs {
   const uint64_t* rk; const uint32_t* rv; const uint32_t* rcnt; const uint32_t* rflag;
   const uint64_t* sk; const uint32_t* sv; const uint32_t* scnt; const uint32_t* sflag;
   uint32_t in_cap, buckets;
-  int q;
+  int dshift;              // bin of a pair = (hash >> dshift) & 4095: the 12 bits below the bucket prefix
   const uint64_t* roff; const uint8_t* rchars;  // string key storage (row-id indexed)
   const uint64_t* soff; const uint8_t* schars;
   uint32_t* out_r; uint32_t* out_s;
@@ -96,9 +96,7 @@ bucket_join_kernel(const BJArgs A) {
     }
   }
   for (int i = tid; i <= BJ_BINS; i += BJ_THREADS) s_bin[i] = 0;
-  const int pshift = 64 - A.q;
-  const int s = max(0, pshift - 12);
-  const uint64_t kbase = (uint64_t)b << pshift;
+  const int s = A.dshift;
   __syncthreads();
 
   // ---- S: counting sort on the 12 bits below the prefix
@@ -107,7 +105,7 @@ bucket_join_kernel(const BJArgs A) {
 #pragma unroll
     for (int k = 0; k < BJ_ITEMS; ++k) {
       const uint32_t i = tid + k * BJ_THREADS;
-      if (i < ns) slot[k] = (uint16_t)atomicAdd(&s_bin[(uint32_t)((skey[k] - kbase) >> s)], 1u);
+      if (i < ns) slot[k] = (uint16_t)atomicAdd(&s_bin[((uint32_t)(skey[k] >> s) & (BJ_BINS - 1))], 1u);
     }
     __syncthreads();
     {
@@ -142,7 +140,7 @@ bucket_join_kernel(const BJArgs A) {
     for (int k = 0; k < BJ_ITEMS; ++k) {
       const uint32_t i = tid + k * BJ_THREADS;
       if (i < ns) {
-        const uint32_t p = s_bin[(uint32_t)((skey[k] - kbase) >> s)] + slot[k];
+        const uint32_t p = s_bin[((uint32_t)(skey[k] >> s) & (BJ_BINS - 1))] + slot[k];
         s_keys[p] = skey[k];
         s_vals[p] = srow[k];
       }
@@ -191,7 +189,7 @@ bucket_join_kernel(const BJArgs A) {
     cnt[k] = 0;
     hit[k] = 0;
     if (i < nr) {
-      const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+      const uint32_t d = ((uint32_t)(rkey[k] >> s) & (BJ_BINS - 1));
       const uint32_t b0 = s_bin[d], n = s_bin[d + 1] - b0;
       uint32_t c = 0, first = 0;
       if (KIND == HMJ_KEY_U64) {
@@ -259,7 +257,7 @@ bucket_join_kernel(const BJArgs A) {
         s_os[off] = s_vals[hit[k]];
         ++off;
         if (cnt[k] > 1) {
-          const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+          const uint32_t d = ((uint32_t)(rkey[k] >> s) & (BJ_BINS - 1));
           const uint32_t b1 = s_bin[d + 1];
           for (uint32_t j = (uint32_t)hit[k] + 1; j < b1; ++j) {
             if (!match(rkey[k], rrow[k], j)) continue;
@@ -285,7 +283,7 @@ bucket_join_kernel(const BJArgs A) {
     for (int k = 0; k < BJ_ITEMS; ++k) {
       const uint32_t i = tid + k * BJ_THREADS;
       if (i < nr && cnt[k]) {
-        const uint32_t d = (uint32_t)((rkey[k] - kbase) >> s);
+        const uint32_t d = ((uint32_t)(rkey[k] >> s) & (BJ_BINS - 1));
         const uint32_t b1 = s_bin[d + 1];
         for (uint32_t j = hit[k]; j < b1; ++j) {
           if (!match(rkey[k], rrow[k], j)) continue;
@@ -306,20 +304,25 @@ bucket_join_kernel(const BJArgs A) {
 // result buffers (WS_OUT_R / WS_OUT_S) and *h_num_pairs is their number.
 // kind = HMJ_KEY_U64: r_hash / s_hash are the key columns themselves.  HMJ_KEY_STRING: they are
 // the hash columns and the offsets/chars arrays give the keys for verification.
-int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t nr,
-                         const uint64_t* s_hash, size_t ns, const uint64_t* roff,
+int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const uint32_t* r_rowid,
+                         size_t nr, const uint64_t* s_hash, const uint32_t* s_rowid, size_t ns,
+                         int skip_bits, const uint64_t* roff,
                          const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
                          cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok) {
   *ok = 0;
   if (nr == 0 || ns == 0) return HMJ_OK;
-  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns);
+  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, skip_bits);
   if (p.levels == 0) return HMJ_OK;
+  if ((p.bits[0] > 8 || p.bits[1] > 8) &&
+      ((reinterpret_cast<uintptr_t>(r_hash) | reinterpret_cast<uintptr_t>(s_hash) |
+        reinterpret_cast<uintptr_t>(r_rowid) | reinterpret_cast<uintptr_t>(s_rowid)) & 15) != 0)
+    return HMJ_OK;
   const char* e = getenv("HMJ_JOIN_UNIFORM");
   if (e && atoi(e) == 0) return HMJ_OK;
   cudaStream_t st = ctx->stream;
   hmj_uniform_buckets R, S;
-  HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, nr, 0, p, 0, &R));
-  HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, ns, 0, p, 1, &S));
+  HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, r_rowid, nr, 0, p, 0, &R));
+  HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, s_rowid, ns, 0, p, 1, &S));
   if (ev_partitioned) HMJ_CUDA(ctx, cudaEventRecord(ev_partitioned, st));
 
   // the global pair counter
@@ -330,7 +333,7 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t 
   A.sk = S.keys; A.sv = S.vals; A.scnt = S.counts; A.sflag = S.flag;
   A.in_cap = p.cap_seg;
   A.buckets = R.buckets;
-  A.q = p.qb;
+  A.dshift = 64 - p.skip - p.qb - 12;
   A.roff = roff; A.rchars = rchars; A.soff = soff; A.schars = schars;
   A.total = d_desc;
 

@@ -25,7 +25,7 @@ namespace {
 constexpr int US_THREADS = 256;
 constexpr int US_ITEMS = 16;
 constexpr int US_TILE = US_THREADS * US_ITEMS;
-constexpr int US_MAX_BINS = 256;
+constexpr int US_MAX_BINS = 512;  // 9-bit levels run with the 1024-thread configuration only
 constexpr int US_CURSOR_STRIDE = 1;  // words between cursors (see uniform_plan)
 constexpr size_t US_SMEM = (size_t)US_TILE * 12 + 3 * US_MAX_BINS * 4 + 64;
 
@@ -390,14 +390,15 @@ int uniform_from_env() {
 
 // Final buckets of at most 4096 pairs on average for `n_plan` rows (the larger relation of a
 // join, so that both sides share the bucket numbering); one or two scatter levels of <= 8 bits.
-hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan) {
+hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan, int skip_bits) {
   hmj_uniform_plan p = {};
   const uint32_t cap_seg = (uint32_t)hmj_segment_sort_cap();
   if (uniform_from_env() == 0 || n_plan <= cap_seg) return p;
   int qb = 0;
   while (((n_plan + ((size_t)1 << qb) - 1) >> qb) > 4096) ++qb;
-  if (qb > 16) return p;
+  if (qb > 18 || skip_bits < 0 || skip_bits + qb + 12 > 64) return p;
   p.qb = qb;
+  p.skip = skip_bits;
   p.cap_seg = cap_seg;
   if (qb <= 8) {
     p.levels = 1;
@@ -410,12 +411,14 @@ hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan) {
   return p;
 }
 
-// Scatters (keys_in[i], iota_base + i) into the 2^qb padded buckets of plan `p`.  Bucket b ends
+// Scatters (keys_in[i], vals_in ? vals_in[i] : iota_base + i) into the 2^qb padded buckets of
+// plan `p` (bucket = the qb hash bits below the p.skip topmost ones).  Bucket b ends
 // up at out->keys/vals[b * cap_seg ...] with out->counts[b] pairs; *out->flag != 0 (device)
 // means a region overflowed and the buckets are void.  `set` selects the workspace slots so
 // that two relations can be held at once (0 or 1).  Nothing is synchronised.
-int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
-                        const hmj_uniform_plan& p, int set, hmj_uniform_buckets* out) {
+int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in, size_t n,
+                        uint32_t iota_base, const hmj_uniform_plan& p, int set,
+                        hmj_uniform_buckets* out) {
   cudaStream_t st = ctx->stream;
   const uint32_t n32 = (uint32_t)n;
   const uint32_t regions1 = 1u << p.bits[0], buckets = 1u << p.qb;
@@ -446,9 +449,12 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_
   HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
   // bulk copies need 16-byte aligned sources (tile starts are multiples of 4096 pairs)
-  const bool tma = uniform_from_env() != 2 && (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0;
+  const bool tma = uniform_from_env() != 2 && (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 &&
+                   (reinterpret_cast<uintptr_t>(vals_in) & 15) == 0;
+  const bool wide = p.bits[0] > 8 || p.bits[1] > 8;  // 512 bins: 1024-thread tiles of 8192 pairs
+  HMJ_ARG(ctx, tma || !wide);
   const char* ecfg = getenv("HMJ_SCATTER_CFG");
-  const int scfg = ecfg ? atoi(ecfg) : 0;
+  const int scfg = wide ? 3 : ecfg ? atoi(ecfg) : 0;
   cudaEvent_t ev;
   // level 1: the raw key column -> 2^bits[0] regions
   const uint32_t tile_items = !tma ? US_TILE : scfg == 1 ? 2048 : scfg == 2 ? 3072 : scfg == 3 ? 8192 : 4096;
@@ -472,14 +478,14 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_
   uint32_t* v_out1 = p.levels == 2 ? d_v1 : d_v2;
   const uint32_t cap_out1 = p.levels == 2 ? cap1 : p.cap_seg;
   if (tiles) {
-    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
+    HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * (vals_in ? 24.0 : 20.0), &ev));
     if (tma)
-      HMJ_TMA_DISPATCH(tiles, keys_in, nullptr, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
-                       64 - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
+      HMJ_TMA_DISPATCH(tiles, keys_in, vals_in, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
+                       64 - p.skip - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
     else
       bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
-          keys_in, nullptr, nullptr, 0, n32, tiles, iota_base, k_out1, v_out1, 64 - p.bits[0],
-          p.bits[0], cap_out1, d_cur1, d_flag);
+          keys_in, vals_in, nullptr, 0, n32, tiles, iota_base, k_out1, v_out1,
+          64 - p.skip - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
     HMJ_LAUNCHED(ctx);
     hmj_prof_end(ctx, ev);
   }
@@ -488,11 +494,11 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
     if (tma)
       HMJ_TMA_DISPATCH(regions1 * tpr, d_k1, d_v1, d_cur1, cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2,
-                       64 - p.qb, p.bits[1], p.cap_seg, d_cur2, d_flag);
+                       64 - p.skip - p.qb, p.bits[1], p.cap_seg, d_cur2, d_flag);
     else
       bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
-          d_k1, d_v1, d_cur1, cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.qb, p.bits[1], p.cap_seg,
-          d_cur2, d_flag);
+          d_k1, d_v1, d_cur1, cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.skip - p.qb, p.bits[1],
+          p.cap_seg, d_cur2, d_flag);
     HMJ_LAUNCHED(ctx);
     hmj_prof_end(ctx, ev);
   }
@@ -512,11 +518,12 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
                          uint64_t* keys_out, uint32_t* vals_out, int* ok) {
   *ok = 0;
   if (keys_in == keys_out) return HMJ_OK;
-  const hmj_uniform_plan p = hmj_uniform_plan_for(n);
-  if (p.levels == 0) return HMJ_OK;
+  const hmj_uniform_plan p = hmj_uniform_plan_for(n, 0);
+  if (p.levels == 0 || p.qb > 16) return HMJ_OK;
+  if ((reinterpret_cast<uintptr_t>(keys_in) & 15) != 0 && (p.bits[0] > 8 || p.bits[1] > 8)) return HMJ_OK;
   cudaStream_t st = ctx->stream;
   hmj_uniform_buckets B;
-  HMJ_TRY(hmj_uniform_scatter(ctx, keys_in, n, iota_base, p, 0, &B));
+  HMJ_TRY(hmj_uniform_scatter(ctx, keys_in, nullptr, n, iota_base, p, 0, &B));
   bucket_offsets_kernel<<<1, 1024, 0, st>>>(B.counts, B.buckets, B.offsets);
   HMJ_LAUNCHED(ctx);
   cudaEvent_t ev;

@@ -167,6 +167,7 @@ struct hmj_uniform_plan {
   int levels;        // 0 = not eligible
   int bits[2];
   int qb;            // total prefix bits = bits[0] + bits[1]
+  int skip;          // topmost hash bits shared by all rows (multi-GPU hash range), not used
   uint32_t cap_seg;  // slots per final bucket
 };
 struct hmj_uniform_buckets {
@@ -177,12 +178,14 @@ struct hmj_uniform_buckets {
   uint32_t* flag;     // != 0: a region overflowed
   uint32_t buckets;
 };
-hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan);
-int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
-                        const hmj_uniform_plan& p, int set, hmj_uniform_buckets* out);
+hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan, int skip_bits);
+int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in, size_t n,
+                        uint32_t iota_base, const hmj_uniform_plan& p, int set,
+                        hmj_uniform_buckets* out);
 // bucket_join.cu
-int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, size_t nr,
-                         const uint64_t* s_hash, size_t ns, const uint64_t* roff,
+int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const uint32_t* r_rowid,
+                         size_t nr, const uint64_t* s_hash, const uint32_t* s_rowid, size_t ns,
+                         int skip_bits, const uint64_t* roff,
                          const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
                          cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok);
 int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,

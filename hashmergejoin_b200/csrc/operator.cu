@@ -37,7 +37,7 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   {
     // uniform hashes: partition both sides on the same hash bits, join bucket by bucket
     int ok = 0;
-    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_U64, d_rkeys, nr, d_skeys, ns, nullptr, nullptr,
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_U64, d_rkeys, nullptr, nr, d_skeys, nullptr, ns, 0, nullptr, nullptr,
                                  nullptr, nullptr, ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
       ctx->tm.sort_uniform += 2;
@@ -51,6 +51,48 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   HMJ_TRY(sort_side_u64(ctx, d_rkeys, nr, WS_R_HASH, WS_R_ROWID, &h, &rid));
   R.d_hash = h; R.d_rowid = rid; R.n = nr; R.key_kind = HMJ_KEY_U64;
   HMJ_TRY(sort_side_u64(ctx, d_skeys, ns, WS_S_HASH, WS_S_ROWID, &h, &rid));
+  S.d_hash = h; S.d_rowid = rid; S.n = ns; S.key_kind = HMJ_KEY_U64;
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
+  HMJ_TRY(join_sorted(ctx, &R, &S, h_num_pairs));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint32_t* d_rrowid,
+                              size_t nr, const uint64_t* d_shash, const uint32_t* d_srowid,
+                              size_t ns, int prefix_bits, uint64_t* h_num_pairs) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, h_num_pairs != nullptr && prefix_bits >= 0 && prefix_bits <= 16);
+  HMJ_ARG(ctx, (nr == 0 || (d_rhash && d_rrowid)) && (ns == 0 || (d_shash && d_srowid)));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->tm.sort_passes = 0;
+  ctx->tm.sort_finishes = 0;
+  ctx->tm.sort_fallbacks = 0;
+  ctx->tm.sort_uniform = 0;
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
+  {
+    int ok = 0;
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_U64, d_rhash, d_rrowid, nr, d_shash, d_srowid, ns,
+                                 prefix_bits, nullptr, nullptr, nullptr, nullptr,
+                                 ctx->ev[EV_SORTED], h_num_pairs, &ok));
+    if (ok) {
+      ctx->tm.sort_uniform += 2;
+      HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
+      return HMJ_OK;
+    }
+  }
+  // skewed hashes: stable sort of both pair relations, then the merge join
+  hmj_relation R = {}, S = {};
+  uint64_t* h = nullptr;
+  uint32_t* rid = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_R_HASH, nr, &h));
+  HMJ_TRY(hmj_ws(ctx, WS_R_ROWID, nr, &rid));
+  HMJ_TRY(hmj_impl_sort(ctx, d_rhash, d_rrowid, nr, h, rid));
+  R.d_hash = h; R.d_rowid = rid; R.n = nr; R.key_kind = HMJ_KEY_U64;
+  HMJ_TRY(hmj_ws(ctx, WS_S_HASH, ns, &h));
+  HMJ_TRY(hmj_ws(ctx, WS_S_ROWID, ns, &rid));
+  HMJ_TRY(hmj_impl_sort(ctx, d_shash, d_srowid, ns, h, rid));
   S.d_hash = h; S.d_rowid = rid; S.n = ns; S.key_kind = HMJ_KEY_U64;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
   HMJ_TRY(join_sorted(ctx, &R, &S, h_num_pairs));
@@ -84,7 +126,7 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
   {
     int ok = 0;
-    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nr, st, ns, d_roffsets, d_rchars,
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nullptr, nr, st, nullptr, ns, 0, d_roffsets, d_rchars,
                                  d_soffsets, d_schars, ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
       ctx->tm.sort_uniform += 2;

@@ -79,9 +79,11 @@ class DistJoin:
         rh, rr = self._exchange_side(rkeys_local, self.rank * nr)
         sh, sr = self._exchange_side(skeys_local, self.rank * ns)
         self.local_rows = (rh.numel(), sh.numel())
-        rh, rr = ctx.sort_pairs(rh, rr, out_hash=rh, out_rowid=rr)
-        sh, sr = ctx.sort_pairs(sh, sr, out_hash=sh, out_rowid=sr)
-        out_r, out_s = ctx.merge_join(SortedRelation(rh, rr), SortedRelation(sh, sr))
         if want_pairs:
+            # staged API (tests: sorted ranges of the ranks concatenate to the global sorted array)
+            rh, rr = ctx.sort_pairs(rh, rr, out_hash=rh, out_rowid=rr)
+            sh, sr = ctx.sort_pairs(sh, sr, out_hash=sh, out_rowid=sr)
+            out_r, out_s = ctx.merge_join(SortedRelation(rh, rr), SortedRelation(sh, sr))
             return out_r.numel(), (out_r, out_s, rh, sh)
-        return out_r.numel()
+        # the rank's hash range shares its top log2(G) bits: bucket join below them
+        return ctx.join_pairs(rh, rr, sh, sr, prefix_bits=self.bits)

@@ -124,6 +124,13 @@ int hmj_merge_join_aggregate(hmj_ctx* ctx, const hmj_relation* r, const hmj_rela
  * until the next join on this context.  *h_num_pairs receives the pair count. */
 int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr, const uint64_t* d_skeys,
                  size_t ns, uint64_t* h_num_pairs);
+/* The local step of the multi-GPU join: two UNSORTED relations of (hash, global
+ * row id) pairs as they arrive from the hash-range exchange.  All hashes share their topmost
+ * `prefix_bits` bits (the rank's hash range, partitioned_hash.h:59 h >> (64 - bits)); identity
+ * hash, so equal hashes are equal keys.  Result as hmj_join_u64 (hmj_join_result*). */
+int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint32_t* d_rrowid, size_t nr,
+                   const uint64_t* d_shash, const uint32_t* d_srowid, size_t ns, int prefix_bits,
+                   uint64_t* h_num_pairs);
 int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
                      size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars, size_t ns,
                      uint64_t* h_num_pairs);

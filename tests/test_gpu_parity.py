@@ -335,6 +335,38 @@ def test_operator_shapes_fall_back_or_not(ctx, oracle, nr, ns, rng_hi):
                        rng.integers(0, rng_hi, size=ns, dtype=np.uint64))
 
 
+def test_join_pairs_of_one_hash_range(ctx, oracle):
+    # the local step of the multi-GPU join: unsorted (hash, global row id) pairs whose hashes share
+    # their top bits (rank 2 of 4)
+    rng = np.random.default_rng(43)
+    n = 700000
+    keys = (datagen.unique_u64(n, seed=9) >> np.uint64(2)) | (np.uint64(2) << np.uint64(62))
+    rk, sk = datagen.permuted(keys, 1).copy(), datagen.permuted(keys, 2)[: n // 2].copy()
+    rk[:1000] = rk[1000:2000]  # some duplicates on the build side
+    rid = (rng.permutation(n) + 5 * n).astype(np.uint32)
+    sid = (rng.permutation(sk.size) + 9 * n).astype(np.uint32)
+    for bits in (2, 0):
+        m = ctx.join_pairs(dev(rk), dev(rid), dev(sk), dev(sid), prefix_bits=bits)
+        # prefix 0 declares no shared bits: the range fills a quarter of the buckets, they overflow
+        # and the stable sort + merge join takes over -- same result
+        assert ctx.timings()["sort_uniform"] == (2 if bits == 2 else 0)
+        out_r, out_s = ctx.join_result_to_host(m)
+        t_r, t_s, _ = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+        e_r, e_s = oracle.sort_pairs(rid[t_r], sid[t_s])
+        c_r, c_s = oracle.sort_pairs(out_r, out_s)
+        assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
+    # skewed range (everything in one bucket): stable sort + merge join
+    rk2 = (rng.integers(0, 1 << 20, size=50000, dtype=np.uint64)) | (np.uint64(2) << np.uint64(62))
+    sk2 = (rng.integers(0, 1 << 20, size=60000, dtype=np.uint64)) | (np.uint64(2) << np.uint64(62))
+    m = ctx.join_pairs(dev(rk2), dev(rid[:50000].copy()), dev(sk2), dev(sid[:60000].copy()), prefix_bits=2)
+    assert ctx.timings()["sort_uniform"] == 0
+    out_r, out_s = ctx.join_result_to_host(m)
+    t_r, t_s, _ = oracle.full_join(Keys(u64=rk2), Keys(u64=sk2))
+    e_r, e_s = oracle.sort_pairs(rid[:50000][t_r], sid[:60000][t_s])
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
+
+
 def test_operator_strings_bucket_join(ctx, oracle):
     off, chars, _, _ = datagen.strgen(50000, seed=7, shuffle_seed=1)
     rng = np.random.default_rng(4)
