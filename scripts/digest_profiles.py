@@ -85,17 +85,26 @@ def ncu_full(tag):
     json.dump({"capture": "ncu --set full --clock-control none --import-source on; bench.py --workload mid "
                           "(64M x 64M u64 keys)", "kernels": per_kernel},
               open(os.path.join(PROF, f"{tag}_ncu_full.json"), "w"), indent=1)
-    # DRAM traffic per onesweep launch for bench.py's roofline.traffic (middle passes: 24 B/pair)
-    ones = [d for k, v in per_kernel.items() if k.startswith("onesweep") for d in v]
-    if ones:
-        def num(s):
-            v, u = s.split()[0], s.split()[1]
-            return float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(u, 1)
-        tr = sorted(num(d["dram__bytes_read.sum"]) + num(d["dram__bytes_write.sum"]) for d in ones)
-        json.dump({"kernel": "onesweep_pass_kernel", "source": f"profiles/{tag}_ncu_full.json",
-                   "dram_bytes_per_launch": tr[len(tr) // 2],
-                   "algorithmic_bytes_per_launch": 64 * 2 ** 20 * 24.0,
-                   "note": "median over the captured launches of a 64M-pair pass (12 B read + 12 B written per pair)"},
+    # DRAM traffic per launch for bench.py's roofline.traffic, per kernel class: median over the
+    # captured launches; algorithmic bytes of a 64M-row launch (bench.py scales by their ratio)
+    def num(s):
+        v, u = s.split()[0], s.split()[1]
+        return float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}.get(u, 1)
+    n_mid = 64 * 2 ** 20
+    alg = {"onesweep_pass_kernel": n_mid * 24.0, "bucket_scatter_tma_kernel": n_mid * 22.0,
+           "segment_sort_kernel": n_mid * 24.0, "bucket_join_kernel": 2 * n_mid * 12.0 + n_mid * 8.0,
+           "join_tile_kernel": 2 * n_mid * 12.0 + n_mid * 8.0}
+    traffic = {}
+    for k, v in per_kernel.items():
+        base = k.split("<")[0]
+        if base in alg:
+            tr = sorted(num(d["dram__bytes_read.sum"]) + num(d["dram__bytes_write.sum"]) for d in v)
+            traffic[base] = {"dram_bytes_per_launch": tr[len(tr) // 2],
+                             "algorithmic_bytes_per_launch": alg[base], "launches_captured": len(tr)}
+    if traffic:
+        json.dump({"source": f"profiles/{tag}_ncu_full.json",
+                   "note": "ncu --set full on bench.py --workload mid (64M x 64M); bucket_scatter: mean of "
+                           "level 1 (20 B/pair) and level 2 (24 B/pair)", "kernels": traffic},
                   open(os.path.join(PROF, "roofline_traffic.json"), "w"), indent=1)
     # top stalls of the first launch of each kernel
     seen = set()
