@@ -89,6 +89,12 @@ SIGNATURES = {
     "hmj_partition_counts_host": (_I, [_P, _P, _SZ, _I, _P]),
     "hmj_hashjoin_build_probe": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),
     "hmj_get_timings": (_I, [_P, C.POINTER(Timings)]),
+    "hmj_dist_setup": (_I, [_P, _I, _I, _SZ, _P]),
+    "hmj_dist_connect": (_I, [_P, _P]),
+    "hmj_dist_begin": (_I, [_P]),
+    "hmj_dist_scatter": (_I, [_P, _I, _P, _SZ, C.c_uint32]),
+    "hmj_dist_join": (_I, [_P, _U64P, C.POINTER(C.c_int)]),
+    "hmj_dist_teardown": (_I, [_P]),
 }
 
 _lib = None

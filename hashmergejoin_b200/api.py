@@ -178,6 +178,28 @@ class Context:
         self._ck(self.lib.hmj_join_result(self.h, C.byref(pr), C.byref(ps), C.byref(m)))
         return pr.value, ps.value, m.value
 
+    # ---- multi-GPU join, exchange fused into the first scatter level (dist_join.cu)
+    def dist_setup(self, rank, world, rows_total):
+        handles = np.zeros(6 * 64, np.uint8)
+        self._ck(self.lib.hmj_dist_setup(self.h, rank, world, rows_total, _hptr(handles)))
+        return handles
+
+    def dist_connect(self, all_handles):
+        all_handles = np.ascontiguousarray(all_handles, np.uint8)
+        self._ck(self.lib.hmj_dist_connect(self.h, _hptr(all_handles)))
+
+    def dist_begin(self):
+        self._ck(self.lib.hmj_dist_begin(self.h))
+
+    def dist_scatter(self, side, keys, rowid_base):
+        _check_dev(keys, 8)
+        self._ck(self.lib.hmj_dist_scatter(self.h, side, _dptr(keys), keys.numel(), rowid_base))
+
+    def dist_join(self):
+        m, ok = C.c_uint64(), C.c_int()
+        self._ck(self.lib.hmj_dist_join(self.h, C.byref(m), C.byref(ok)))
+        return m.value, ok.value
+
     def join_strings(self, roff, rchars, soff, schars):
         m = C.c_uint64()
         self._ck(self.lib.hmj_join_strings(self.h, _dptr(roff), _dptr(rchars), roff.numel() - 1,

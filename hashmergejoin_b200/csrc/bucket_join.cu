@@ -298,42 +298,24 @@ bucket_join_kernel(const BJArgs A) {
 
 }  // namespace
 
-// Whole-operator join through the uniform path: scatter R and S into the same 2^qb buckets, join
-// bucket by bucket.  *ok = 0 when the inputs are not eligible or a bucket overflowed (the host
-// then sorts both relations and merge-joins them); on success the pairs are in the context's
-// result buffers (WS_OUT_R / WS_OUT_S) and *h_num_pairs is their number.
-// kind = HMJ_KEY_U64: r_hash / s_hash are the key columns themselves.  HMJ_KEY_STRING: they are
-// the hash columns and the offsets/chars arrays give the keys for verification.
-int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const uint32_t* r_rowid,
-                         size_t nr, const uint64_t* s_hash, const uint32_t* s_rowid, size_t ns,
-                         int skip_bits, const uint64_t* roff,
-                         const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
-                         cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok) {
+// Joins the padded buckets of two relations (same bucket numbering).  *ok = 0 when a scatter level
+// overflowed; on success the pairs are in WS_OUT_R / WS_OUT_S and *h_num_pairs is their number.
+int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
+                        const hmj_uniform_buckets& S, uint32_t cap_seg, int dshift, size_t nr,
+                        size_t ns, const uint64_t* roff, const uint8_t* rchars,
+                        const uint64_t* soff, const uint8_t* schars, uint64_t* h_num_pairs,
+                        int* ok) {
   *ok = 0;
-  if (nr == 0 || ns == 0) return HMJ_OK;
-  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, skip_bits);
-  if (p.levels == 0) return HMJ_OK;
-  if ((p.bits[0] > 8 || p.bits[1] > 8) &&
-      ((reinterpret_cast<uintptr_t>(r_hash) | reinterpret_cast<uintptr_t>(s_hash) |
-        reinterpret_cast<uintptr_t>(r_rowid) | reinterpret_cast<uintptr_t>(s_rowid)) & 15) != 0)
-    return HMJ_OK;
-  const char* e = getenv("HMJ_JOIN_UNIFORM");
-  if (e && atoi(e) == 0) return HMJ_OK;
   cudaStream_t st = ctx->stream;
-  hmj_uniform_buckets R, S;
-  HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, r_rowid, nr, 0, p, 0, &R));
-  HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, s_rowid, ns, 0, p, 1, &S));
-  if (ev_partitioned) HMJ_CUDA(ctx, cudaEventRecord(ev_partitioned, st));
-
   // the global pair counter
   uint64_t* d_desc = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_JOIN_TILES, 4, &d_desc));
   BJArgs A = {};
   A.rk = R.keys; A.rv = R.vals; A.rcnt = R.counts; A.rflag = R.flag;
   A.sk = S.keys; A.sv = S.vals; A.scnt = S.counts; A.sflag = S.flag;
-  A.in_cap = p.cap_seg;
+  A.in_cap = cap_seg;
   A.buckets = R.buckets;
-  A.dshift = 64 - p.skip - p.qb - 12;
+  A.dshift = dshift;
   A.roff = roff; A.rchars = rchars; A.soff = soff; A.schars = schars;
   A.total = d_desc;
 
@@ -380,4 +362,33 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const u
     cap = (size_t)m;  // the buckets are still valid: join again into larger buffers
   }
   return hmj_fail(ctx, HMJ_ECAPACITY, "bucket join: result did not fit twice", __FILE__, __LINE__);
+}
+
+// Whole-operator join through the uniform path: scatter R and S into the same 2^qb buckets, join
+// bucket by bucket.  *ok = 0 when the inputs are not eligible or a bucket overflowed (the host
+// then sorts both relations and merge-joins them); on success the pairs are in the context's
+// result buffers (WS_OUT_R / WS_OUT_S) and *h_num_pairs is their number.
+// kind = HMJ_KEY_U64: r_hash / s_hash are the key columns themselves.  HMJ_KEY_STRING: they are
+// the hash columns and the offsets/chars arrays give the keys for verification.
+int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const uint32_t* r_rowid,
+                         size_t nr, const uint64_t* s_hash, const uint32_t* s_rowid, size_t ns,
+                         int skip_bits, const uint64_t* roff,
+                         const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
+                         cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok) {
+  *ok = 0;
+  if (nr == 0 || ns == 0) return HMJ_OK;
+  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, skip_bits);
+  if (p.levels == 0) return HMJ_OK;
+  if ((p.bits[0] > 8 || p.bits[1] > 8) &&
+      ((reinterpret_cast<uintptr_t>(r_hash) | reinterpret_cast<uintptr_t>(s_hash) |
+        reinterpret_cast<uintptr_t>(r_rowid) | reinterpret_cast<uintptr_t>(s_rowid)) & 15) != 0)
+    return HMJ_OK;
+  const char* e = getenv("HMJ_JOIN_UNIFORM");
+  if (e && atoi(e) == 0) return HMJ_OK;
+  hmj_uniform_buckets R, S;
+  HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, r_rowid, nr, 0, p, 0, &R));
+  HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, s_rowid, ns, 0, p, 1, &S));
+  if (ev_partitioned) HMJ_CUDA(ctx, cudaEventRecord(ev_partitioned, ctx->stream));
+  return hmj_bucket_join_run(ctx, kind, R, S, p.cap_seg, 64 - p.skip - p.qb - 12, nr, ns, roff,
+                             rchars, soff, schars, h_num_pairs, ok);
 }

@@ -149,7 +149,7 @@ template <int THREADS>
 struct UtCfg {
   static constexpr int TILE = THREADS * UT_ITEMS;
   static constexpr size_t BUF_BYTES = (size_t)TILE * 12;
-  static constexpr size_t SMEM = 2 * BUF_BYTES + 4 * US_MAX_BINS * 4 + 32 * 4 + 64;
+  static constexpr size_t SMEM = 2 * BUF_BYTES + 4 * US_MAX_BINS * 4 + 32 * 4 + 64 + 16 * 8;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -185,14 +185,20 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
       : "memory");
 }
 
-template <int UT_THREADS, int MIN_BLOCKS>
+// DIST: the destination regions are spread over the GPUs of the job (multi-GPU level 1, the
+// exchange step of SURVEY.md 8e fused into the scatter): region g of the 2^bits belongs to GPU
+// g >> own_bits, its cursor and slots live in that GPU's memory and are reached through peer
+// pointers (NVLink): system-scope atomicAdd for the reservation, plain stores for the runs.
+
+template <int UT_THREADS, int MIN_BLOCKS, bool DIST>
 __global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
 bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           const uint32_t* __restrict__ in_counts, uint32_t in_stride,
                           uint32_t n_single, uint32_t tiles_per_region, uint32_t total_tiles,
                           uint32_t iota_base, uint64_t* __restrict__ keys_out,
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
-                          uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag) {
+                          uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag,
+                          const hmj_peer_regions peers) {
   constexpr int UT_TILE = UtCfg<UT_THREADS>::TILE;
   constexpr size_t UT_BUF_BYTES = UtCfg<UT_THREADS>::BUF_BYTES;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -202,8 +208,14 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
   uint32_t* s_rcount = s_gbase + US_MAX_BINS;  // [regions <= 256] pairs per input region
   uint32_t* s_scan = s_rcount + US_MAX_BINS;   // [32]
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_scan + 32);  // [2]
+  uint64_t** s_pk = reinterpret_cast<uint64_t**>(s_bar + 2);   // [8] peer key columns (DIST)
+  uint32_t** s_pv = reinterpret_cast<uint32_t**>(s_pk + 8);    // [8] peer row-id columns
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (DIST && tid < 8) {
+    s_pk[tid] = peers.keys[tid];
+    s_pv[tid] = peers.vals[tid];
+  }
   const int bins = 1 << bits;
   const uint32_t mask = (uint32_t)bins - 1;
   if (tid == 0) {
@@ -291,7 +303,14 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     if (tid < bins) {
       c = s_cnt[tid];
       bucket = ((t / tiles_per_region) << bits) | (uint32_t)tid;
-      if (c) old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
+      if (DIST) {
+        // level 1 of the job: bucket == tid; owner GPU and its local region index
+        const uint32_t local = bucket & ((1u << peers.own_bits) - 1);
+        if (c) old = atomicAdd_system(peers.cursors[bucket >> peers.own_bits] + local, c);
+        bucket = local;
+      } else if (c) {
+        old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
+      }
     }
     uint32_t val[UT_ITEMS];
 #pragma unroll
@@ -337,9 +356,16 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll 4
     for (uint32_t i = tid; i < valid; i += UT_THREADS) {
       const uint64_t kk = b_keys[i];
-      const uint32_t dst = s_gbase[(uint32_t)(kk >> shift) & mask] + i;
-      keys_out[dst] = kk;
-      vals_out[dst] = b_vals[i];
+      const uint32_t d = (uint32_t)(kk >> shift) & mask;
+      const uint32_t dst = s_gbase[d] + i;
+      if (DIST) {
+        const uint32_t o = d >> peers.own_bits;
+        s_pk[o][dst] = kk;
+        s_pv[o][dst] = b_vals[i];
+      } else {
+        keys_out[dst] = kk;
+        vals_out[dst] = b_vals[i];
+      }
     }
     __syncthreads();  // the buffer may be refilled from here on
   }
@@ -461,11 +487,11 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
   const uint32_t tiles = (uint32_t)hmj_div_up(n, tile_items);
 #define HMJ_TMA_LAUNCH(T, B, NT, ...)                                                              \
   do {                                                                                            \
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<T, B>,                           \
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<T, B, false>,                    \
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,               \
                                        (int)UtCfg<T>::SMEM));                                     \
-    bucket_scatter_tma_kernel<T, B><<<min((uint32_t)(NT), (uint32_t)ctx->num_sms * B), T,         \
-                                      UtCfg<T>::SMEM, st>>>(__VA_ARGS__);                         \
+    bucket_scatter_tma_kernel<T, B, false><<<min((uint32_t)(NT), (uint32_t)ctx->num_sms * B), T,  \
+                                             UtCfg<T>::SMEM, st>>>(__VA_ARGS__, hmj_peer_regions()); \
   } while (0)
 #define HMJ_TMA_DISPATCH(NT, ...)                                     \
   do {                                                               \
@@ -535,5 +561,58 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
   HMJ_CUDA(ctx, cudaMemcpyAsync(h, B.flag, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
   HMJ_CUDA(ctx, cudaStreamSynchronize(st));
   *ok = h[0] == 0;
+  return HMJ_OK;
+}
+
+// ---- launch helpers of the multi-GPU join (dist_join.cu) --------------------------------
+// Level 1 of the job on this rank's rows: regions are spread over the GPUs (peer pointers).
+int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                            int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
+                            uint32_t* d_flag) {
+  if (n == 0) return HMJ_OK;
+  HMJ_ARG(ctx, (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 && bits <= 9);
+  cudaStream_t st = ctx->stream;
+  cudaEvent_t ev;
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
+  if (bits > 8) {
+    const uint32_t tiles = (uint32_t)hmj_div_up(n, UtCfg<1024>::TILE);
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<1024, 1, true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)UtCfg<1024>::SMEM));
+    bucket_scatter_tma_kernel<1024, 1, true><<<min(tiles, (uint32_t)ctx->num_sms), 1024,
+                                               UtCfg<1024>::SMEM, st>>>(
+        keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
+        bits, out_cap, nullptr, d_flag, peers);
+  } else {
+    const uint32_t tiles = (uint32_t)hmj_div_up(n, UtCfg<512>::TILE);
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<512, 2, true>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)UtCfg<512>::SMEM));
+    bucket_scatter_tma_kernel<512, 2, true><<<min(tiles, (uint32_t)ctx->num_sms * 2), 512,
+                                              UtCfg<512>::SMEM, st>>>(
+        keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
+        bits, out_cap, nullptr, d_flag, peers);
+  }
+  HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev);
+  return HMJ_OK;
+}
+
+// Level 2 on this rank's own regions (`regions` of `cap1` slots, counts in cur1) -> padded
+// final buckets (bucket = (region << bits) | digit).
+int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
+                       uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
+                       uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
+                       uint32_t* d_flag) {
+  cudaStream_t st = ctx->stream;
+  const int scfg = bits > 8 ? 3 : 0;
+  const uint32_t tile_items = bits > 8 ? 8192 : 4096;
+  const uint32_t tpr = (uint32_t)hmj_div_up(cap1, tile_items);
+  cudaEvent_t ev;
+  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n_hint * 24.0, &ev));
+  HMJ_TMA_DISPATCH(regions * tpr, k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits,
+                   cap_seg, cur2, d_flag);
+  HMJ_LAUNCHED(ctx);
+  hmj_prof_end(ctx, ev);
   return HMJ_OK;
 }

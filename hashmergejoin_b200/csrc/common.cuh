@@ -70,6 +70,8 @@ struct hmj_ctx {
   std::vector<int> prof_kind;            // kernel class of pair i (hmj_kernel_class)
   std::vector<double> prof_bytes;        // algorithmic bytes of launch i
   size_t prof_used = 0;
+  // multi-GPU join state (dist_join.cu)
+  struct hmj_dist_state* dist = nullptr;
   // last whole-operator result
   uint64_t last_pairs = 0;
   hmj_timings tm;
@@ -163,6 +165,20 @@ int hmj_launch_bucket_finish(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, const
                              const uint32_t* offsets, uint32_t buckets, uint32_t in_cap, int q,
                              uint64_t* out_keys, uint32_t* out_vals, uint32_t* d_flag);
 // bucket_scatter.cu
+// regions of a scatter level that live on the GPUs of a multi-GPU job (peer pointers)
+struct hmj_peer_regions {
+  uint64_t* keys[8];
+  uint32_t* vals[8];
+  uint32_t* cursors[8];
+  int own_bits;  // log2(regions per GPU)
+};
+int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
+                            int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
+                            uint32_t* d_flag);
+int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
+                       uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
+                       uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
+                       uint32_t* d_flag);
 struct hmj_uniform_plan {
   int levels;        // 0 = not eligible
   int bits[2];
@@ -188,6 +204,11 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const u
                          int skip_bits, const uint64_t* roff,
                          const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
                          cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok);
+int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
+                        const hmj_uniform_buckets& S, uint32_t cap_seg, int dshift, size_t nr,
+                        size_t ns, const uint64_t* roff, const uint8_t* rchars,
+                        const uint64_t* soff, const uint8_t* schars, uint64_t* h_num_pairs,
+                        int* ok);
 int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                          uint64_t* keys_out, uint32_t* vals_out, int* ok);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,

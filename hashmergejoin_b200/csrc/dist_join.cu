@@ -1,0 +1,194 @@
+// dist_join.cu -- multi-GPU hash-merge join with the exchange FUSED into the first scatter level.
+//
+// every GPU splits its rows of R and S by hash range, one exchange moves range g
+// to GPU g, then every GPU joins its own range.  Here the split and the exchange are one kernel:
+// level 1 of the bucket scatter (bucket_scatter.cu) runs over the GPU's local rows with its
+// 2^b1 destination regions spread over the GPUs of the job -- region r belongs to GPU
+// r >> (b1 - log2 G) -- and writes every run straight into the owner's memory through NVLink peer
+// pointers (slot reservation = one system-scope atomicAdd on the owner's cursor).  No partition
+// pass, no send buffers, no NCCL all-to-all; after a barrier every GPU continues locally with
+// level 2 and the bucket join on hash bits below the ones that chose the GPU.  It stands in for
+// partition_only's per-thread push_back into shared partitions (partitioned_hash.h:82-124) at
+// the scale of a node.
+//
+// One process per GPU: the regions are cudaMalloc'ed here and shared with CUDA IPC handles that
+// the caller exchanges over torch.distributed (hashmergejoin_b200/dist.py).
+#include <math.h>
+
+#include "common.cuh"
+
+struct hmj_dist_state {
+  int world = 1, rank = 0;
+  int g_bits = 0, b1 = 0, b2 = 0, own_bits = 0;  // level-1 bits (job wide), level-2 bits, log2(own regions)
+  uint32_t cap1 = 0, cap_seg = 0, regions_own = 0;
+  // own level-1 regions per side (0 = R, 1 = S): keys, row ids, cursors (+ 8 words: [regions_own] = flag)
+  uint64_t* k1[2] = {nullptr, nullptr};
+  uint32_t* v1[2] = {nullptr, nullptr};
+  uint32_t* c1[2] = {nullptr, nullptr};
+  hmj_peer_regions peers[2];
+  void* opened[2][8][3] = {};
+  size_t rows_total = 0;
+};
+
+namespace {
+constexpr int HANDLE_BYTES = 64;  // sizeof(cudaIpcMemHandle_t)
+static_assert(sizeof(cudaIpcMemHandle_t) == HANDLE_BYTES, "IPC handle size");
+}  // namespace
+
+// Plans the job for `rows_total` rows per relation over `world` GPUs, allocates this rank's
+// level-1 regions and writes their 6 IPC handles (R keys, R row ids, R cursors, S ...) to
+// handles_out[6 * 64].
+extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_total,
+                              unsigned char* handles_out) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, world >= 2 && world <= 8 && (world & (world - 1)) == 0 && rank >= 0 && rank < world);
+  HMJ_ARG(ctx, handles_out != nullptr && ctx->dist == nullptr);
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  hmj_dist_state* d = new hmj_dist_state();
+  d->world = world;
+  d->rank = rank;
+  d->rows_total = rows_total;
+  while ((1 << d->g_bits) < world) ++d->g_bits;
+  int total_bits = 0;
+  while (((rows_total + ((size_t)1 << total_bits) - 1) >> total_bits) > 4096) ++total_bits;
+  if (total_bits > 18 || total_bits < d->g_bits + 2) {
+    delete d;
+    return hmj_fail(ctx, HMJ_EARG, "dist join: rows_total outside the supported range", __FILE__, __LINE__);
+  }
+  d->b1 = (total_bits + 1) / 2;
+  if (d->b1 < d->g_bits + 1) d->b1 = d->g_bits + 1;
+  d->b2 = total_bits - d->b1;
+  d->own_bits = d->b1 - d->g_bits;
+  d->regions_own = 1u << d->own_bits;
+  const double avg1 = (double)rows_total / (double)(1u << d->b1);
+  d->cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
+  d->cap_seg = (uint32_t)hmj_segment_sort_cap();
+  for (int s = 0; s < 2; ++s) {
+    const size_t slots = (size_t)d->regions_own * d->cap1;
+    HMJ_CUDA(ctx, cudaMalloc(&d->k1[s], slots * 8));
+    HMJ_CUDA(ctx, cudaMalloc(&d->v1[s], slots * 4));
+    HMJ_CUDA(ctx, cudaMalloc(&d->c1[s], ((size_t)d->regions_own + 8) * 4));
+    HMJ_CUDA(ctx, cudaMemset(d->c1[s], 0, ((size_t)d->regions_own + 8) * 4));
+    void* ptrs[3] = {d->k1[s], d->v1[s], d->c1[s]};
+    for (int j = 0; j < 3; ++j) {
+      cudaIpcMemHandle_t h;
+      HMJ_CUDA(ctx, cudaIpcGetMemHandle(&h, ptrs[j]));
+      memcpy(handles_out + (size_t)(s * 3 + j) * HANDLE_BYTES, &h, HANDLE_BYTES);
+    }
+  }
+  ctx->dist = d;
+  return HMJ_OK;
+}
+
+// all_handles[world][6][64]: what every rank wrote in hmj_dist_setup, in rank order.
+extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, ctx->dist != nullptr && all_handles != nullptr);
+  hmj_dist_state* d = ctx->dist;
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  for (int s = 0; s < 2; ++s) {
+    memset(&d->peers[s], 0, sizeof d->peers[s]);
+    d->peers[s].own_bits = d->own_bits;
+    for (int r = 0; r < d->world; ++r) {
+      void* ptrs[3];
+      if (r == d->rank) {
+        ptrs[0] = d->k1[s]; ptrs[1] = d->v1[s]; ptrs[2] = d->c1[s];
+      } else {
+        for (int j = 0; j < 3; ++j) {
+          cudaIpcMemHandle_t h;
+          memcpy(&h, all_handles + ((size_t)r * 6 + s * 3 + j) * HANDLE_BYTES, HANDLE_BYTES);
+          HMJ_CUDA(ctx, cudaIpcOpenMemHandle(&ptrs[j], h, cudaIpcMemLazyEnablePeerAccess));
+          d->opened[s][r][j] = ptrs[j];
+        }
+      }
+      d->peers[s].keys[r] = reinterpret_cast<uint64_t*>(ptrs[0]);
+      d->peers[s].vals[r] = reinterpret_cast<uint32_t*>(ptrs[1]);
+      d->peers[s].cursors[r] = reinterpret_cast<uint32_t*>(ptrs[2]);
+    }
+  }
+  return HMJ_OK;
+}
+
+// Zeroes this rank's cursors and flags.  Every rank must have done so (and synchronised) before
+// any rank scatters: the caller puts a barrier after it.
+extern "C" int hmj_dist_begin(hmj_ctx* ctx) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, ctx->dist != nullptr);
+  hmj_dist_state* d = ctx->dist;
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  for (int s = 0; s < 2; ++s)
+    HMJ_CUDA(ctx, cudaMemsetAsync(d->c1[s], 0, ((size_t)d->regions_own + 8) * 4, ctx->stream));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return HMJ_OK;
+}
+
+// Level 1 over this rank's rows of relation `side` (global row ids rowid_base + i), written into
+// the regions of all ranks.  Returns after the kernel has completed (its peer writes are then
+// visible to their owners once the caller's barrier has passed).
+extern "C" int hmj_dist_scatter(hmj_ctx* ctx, int side, const uint64_t* d_keys, size_t n,
+                                uint32_t rowid_base) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, ctx->dist != nullptr && (side == 0 || side == 1) && (n == 0 || d_keys));
+  hmj_dist_state* d = ctx->dist;
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  uint32_t* flag = d->c1[side] + d->regions_own;
+  HMJ_TRY(hmj_scatter_level1_dist(ctx, d_keys, n, rowid_base, 64 - d->b1, d->b1, d->cap1,
+                                  d->peers[side], flag));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return HMJ_OK;
+}
+
+// Level 2 + bucket join on this rank's hash range.  *ok = 0: some region or bucket overflowed on
+// this rank (the caller agrees on that across ranks and falls back to the NCCL path).
+extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, ctx->dist != nullptr && h_num_pairs && ok);
+  hmj_dist_state* d = ctx->dist;
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  *ok = 0;
+  *h_num_pairs = 0;
+  const uint32_t buckets = d->regions_own << d->b2;
+  const size_t n_hint = d->rows_total / d->world;
+  hmj_uniform_buckets B[2];
+  for (int s = 0; s < 2; ++s) {
+    uint32_t* words = nullptr;
+    HMJ_TRY(hmj_ws(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, (size_t)buckets + 8, &words));
+    HMJ_CUDA(ctx, cudaMemsetAsync(words, 0, ((size_t)buckets + 8) * 4, st));
+    uint64_t* k2 = nullptr;
+    uint32_t* v2 = nullptr;
+    const size_t slots2 = (size_t)buckets * d->cap_seg;
+    HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, slots2, &k2));
+    HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, slots2, &v2));
+    uint32_t* flag = d->c1[s] + d->regions_own;  // level-1 overflows of this rank's regions land here too
+    HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, d->regions_own, n_hint,
+                               64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag));
+    B[s].keys = k2;
+    B[s].vals = v2;
+    B[s].counts = words + 8;
+    B[s].offsets = nullptr;
+    B[s].flag = flag;
+    B[s].buckets = buckets;
+  }
+  return hmj_bucket_join_run(ctx, HMJ_KEY_U64, B[0], B[1], d->cap_seg, 64 - d->b1 - d->b2 - 12,
+                             n_hint, n_hint, nullptr, nullptr, nullptr, nullptr, h_num_pairs, ok);
+}
+
+extern "C" int hmj_dist_teardown(hmj_ctx* ctx) {
+  if (!ctx) return HMJ_EARG;
+  hmj_dist_state* d = ctx->dist;
+  if (!d) return HMJ_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (int s = 0; s < 2; ++s) {
+    for (int r = 0; r < 8; ++r)
+      for (int j = 0; j < 3; ++j)
+        if (d->opened[s][r][j]) cudaIpcCloseMemHandle(d->opened[s][r][j]);
+    if (d->k1[s]) cudaFree(d->k1[s]);
+    if (d->v1[s]) cudaFree(d->v1[s]);
+    if (d->c1[s]) cudaFree(d->c1[s]);
+  }
+  delete d;
+  ctx->dist = nullptr;
+  return HMJ_OK;
+}

@@ -11,6 +11,7 @@ never straddle ranks.  torch.distributed is plumbing only: NCCL all_to_all_singl
 the kernels run on (gloo on CPU tensors in the world_size-2 host-logic tests).
 """
 import math
+import os
 
 import torch
 import torch.distributed as dist
@@ -56,6 +57,23 @@ class DistJoin:
         self.bits = partition_bits(world)
         self.exchange_bytes = 0      # bytes this rank sent over NVLink in the last join
         self.local_rows = (0, 0)     # (|R|, |S|) of this rank's hash range in the last join
+        # fused path: level 1 of the bucket scatter writes straight into the owners' regions over
+        # NVLink peer memory (CUDA IPC handles exchanged here); needs the job size up front
+        self.fused = False
+        self.fused_joins = 0
+        if world > 1 and rows_total_hint > 0 and dist.get_backend() == "nccl" \
+                and os.environ.get("HMJ_DIST_FUSED", "1") != "0":
+            try:
+                mine = torch.from_numpy(ctx.dist_setup(rank, world, rows_total_hint)).cuda()
+                allh = torch.empty(world * mine.numel(), dtype=torch.uint8, device=mine.device)
+                dist.all_gather_into_tensor(allh, mine)
+                ctx.dist_connect(allh.cpu().numpy())
+                self.fused = True
+            except Exception as e:  # size outside the plan's range: the NCCL path serves it
+                self.fused_error = str(e)
+            flag = torch.tensor([1 if self.fused else 0], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            self.fused = bool(flag.item())
 
     def _exchange_side(self, keys, rowid_base):
         """partition local rows by destination, exchange -> (hash, rowid) tensors of my range"""
@@ -75,6 +93,21 @@ class DistJoin:
         ctx = self.ctx
         nr, ns = rkeys_local.numel(), skeys_local.numel()
         self.exchange_bytes = 0
+        if self.fused and not want_pairs:
+            ctx.dist_begin()
+            dist.barrier()
+            ctx.dist_scatter(0, rkeys_local, self.rank * nr)
+            ctx.dist_scatter(1, skeys_local, self.rank * ns)
+            dist.barrier()
+            m, ok = ctx.dist_join()
+            t = torch.tensor([ok], device=rkeys_local.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            if int(t.item()) == 1:
+                self.fused_joins += 1
+                # uniform hashes: (G-1)/G of the local rows leave the rank, 12 B per pair
+                self.exchange_bytes = 12 * (nr + ns) * (self.world - 1) // self.world
+                self.local_rows = (nr, ns)
+                return m
         # global row ids: rank-major blocks (rank r owns rows [r*n, (r+1)*n) of each relation)
         rh, rr = self._exchange_side(rkeys_local, self.rank * nr)
         sh, sr = self._exchange_side(skeys_local, self.rank * ns)

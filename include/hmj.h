@@ -184,6 +184,21 @@ int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r_unsorted,
                              const hmj_relation* s_unsorted, const uint64_t* d_rvals,
                              const uint64_t* d_svals, uint64_t* h_hits, uint64_t* h_sum);
 
+/* ---- multi-GPU join with the exchange fused into the first scatter level (dist_join.cu) --
+ * One process per GPU.  setup: plan for rows_total rows per relation over `world` GPUs (power of
+ * two, <= 8), allocate this rank's level-1 regions, export their 6 CUDA IPC handles (6 x 64
+ * bytes).  connect: all ranks' handles in rank order (world x 6 x 64 bytes).  Per join:
+ * begin (zero own cursors) -> BARRIER -> scatter(side 0 = R, 1 = S: level 1 over the local rows,
+ * runs written into the owners' memory over NVLink) -> BARRIER -> join (level 2 + bucket join of
+ * the own hash range; *ok = 0 when a region overflowed: every rank then uses the NCCL path).
+ * Replaces partition_only's shared partitions (partitioned_hash.h:82-124) at node scale. */
+int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_total, unsigned char* handles_out);
+int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles);
+int hmj_dist_begin(hmj_ctx* ctx);
+int hmj_dist_scatter(hmj_ctx* ctx, int side, const uint64_t* d_keys, size_t n, uint32_t rowid_base);
+int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok);
+int hmj_dist_teardown(hmj_ctx* ctx);
+
 /* ---- per-stage device timings of the last whole-operator call ------------------------ */
 typedef struct hmj_timings {
   float hash_ms;       /* K1 */
