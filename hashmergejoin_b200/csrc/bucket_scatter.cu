@@ -187,8 +187,12 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
 
 // DIST: the destination regions are spread over the GPUs of the job (multi-GPU level 1, the
 // exchange step of SURVEY.md 8e fused into the scatter): region g of the 2^bits belongs to GPU
-// g >> own_bits, its cursor and slots live in that GPU's memory and are reached through peer
-// pointers (NVLink): system-scope atomicAdd for the reservation, plain stores for the runs.
+// g >> own_bits and lives in that GPU's memory, reached through peer pointers (NVLink) with plain
+// stores.  Every source GPU has its own sub-region in every region, so the slot reservation is
+// an atomicAdd on a LOCAL cursor (remote same-address atomics from all GPUs on one cursor
+// serialise at ~30 ns each and bound the first version of this kernel at 240 GB/s of NVLink).
+// region_shift (level 2 of such a job): input region t / tiles_per_region is a sub-region; the
+// bucket prefix is the region it belongs to, (t / tiles_per_region) >> region_shift.
 
 template <int UT_THREADS, int MIN_BLOCKS, bool DIST>
 __global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
@@ -198,7 +202,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
                           uint32_t iota_base, uint64_t* __restrict__ keys_out,
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
                           uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag,
-                          const hmj_peer_regions peers) {
+                          const hmj_peer_regions peers, int region_shift) {
   constexpr int UT_TILE = UtCfg<UT_THREADS>::TILE;
   constexpr size_t UT_BUF_BYTES = UtCfg<UT_THREADS>::BUF_BYTES;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -302,15 +306,10 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     uint32_t c = 0, old = 0, bucket = 0;
     if (tid < bins) {
       c = s_cnt[tid];
-      bucket = ((t / tiles_per_region) << bits) | (uint32_t)tid;
-      if (DIST) {
-        // level 1 of the job: bucket == tid; owner GPU and its local region index
-        const uint32_t local = bucket & ((1u << peers.own_bits) - 1);
-        if (c) old = atomicAdd_system(peers.cursors[bucket >> peers.own_bits] + local, c);
-        bucket = local;
-      } else if (c) {
-        old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
-      }
+      bucket = (((t / tiles_per_region) >> region_shift) << bits) | (uint32_t)tid;
+      if (c) old = atomicAdd(&cursors[(size_t)bucket * US_CURSOR_STRIDE], c);
+      // DIST (level 1 of the job, bucket == tid): my sub-region of the owner's region
+      if (DIST) bucket = (bucket & ((1u << peers.own_bits) - 1)) * (uint32_t)peers.world + (uint32_t)peers.rank;
     }
     uint32_t val[UT_ITEMS];
 #pragma unroll
@@ -369,6 +368,15 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     }
     __syncthreads();  // the buffer may be refilled from here on
   }
+}
+
+// after the DIST level 1: region r's count of THIS source goes to the owner's count table
+__global__ void push_counts_kernel(const uint32_t* __restrict__ cursors, uint32_t regions,
+                                   const hmj_peer_regions peers) {
+  const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= regions) return;
+  const uint32_t local = r & ((1u << peers.own_bits) - 1);
+  peers.counts[r >> peers.own_bits][local * (uint32_t)peers.world + (uint32_t)peers.rank] = cursors[r];
 }
 
 // exclusive scan of the final bucket counts -> dense output offsets (one CTA; <= 2^18 buckets)
@@ -491,7 +499,7 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
                                        cudaFuncAttributeMaxDynamicSharedMemorySize,               \
                                        (int)UtCfg<T>::SMEM));                                     \
     bucket_scatter_tma_kernel<T, B, false><<<min((uint32_t)(NT), (uint32_t)ctx->num_sms * B), T,  \
-                                             UtCfg<T>::SMEM, st>>>(__VA_ARGS__, hmj_peer_regions()); \
+                                             UtCfg<T>::SMEM, st>>>(__VA_ARGS__, hmj_peer_regions(), 0); \
   } while (0)
 #define HMJ_TMA_DISPATCH(NT, ...)                                     \
   do {                                                               \
@@ -568,7 +576,7 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
 // Level 1 of the job on this rank's rows: regions are spread over the GPUs (peer pointers).
 int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                             int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
-                            uint32_t* d_flag) {
+                            uint32_t* d_cursors, uint32_t* d_flag) {
   if (n == 0) return HMJ_OK;
   HMJ_ARG(ctx, (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 && bits <= 9);
   cudaStream_t st = ctx->stream;
@@ -582,7 +590,7 @@ int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uin
     bucket_scatter_tma_kernel<1024, 1, true><<<min(tiles, (uint32_t)ctx->num_sms), 1024,
                                                UtCfg<1024>::SMEM, st>>>(
         keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
-        bits, out_cap, nullptr, d_flag, peers);
+        bits, out_cap, d_cursors, d_flag, peers, 0);
   } else {
     const uint32_t tiles = (uint32_t)hmj_div_up(n, UtCfg<512>::TILE);
     HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<512, 2, true>,
@@ -591,10 +599,13 @@ int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uin
     bucket_scatter_tma_kernel<512, 2, true><<<min(tiles, (uint32_t)ctx->num_sms * 2), 512,
                                               UtCfg<512>::SMEM, st>>>(
         keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
-        bits, out_cap, nullptr, d_flag, peers);
+        bits, out_cap, d_cursors, d_flag, peers, 0);
   }
   HMJ_LAUNCHED(ctx);
   hmj_prof_end(ctx, ev);
+  // hand my sub-region counts to the owners of the regions
+  push_counts_kernel<<<((1u << bits) + 255) / 256, 256, 0, st>>>(d_cursors, 1u << bits, peers);
+  HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 
@@ -603,15 +614,29 @@ int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uin
 int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
                        uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
                        uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag) {
+                       uint32_t* d_flag, int region_shift) {
   cudaStream_t st = ctx->stream;
-  const int scfg = bits > 8 ? 3 : 0;
   const uint32_t tile_items = bits > 8 ? 8192 : 4096;
   const uint32_t tpr = (uint32_t)hmj_div_up(cap1, tile_items);
   cudaEvent_t ev;
   HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n_hint * 24.0, &ev));
-  HMJ_TMA_DISPATCH(regions * tpr, k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits,
-                   cap_seg, cur2, d_flag);
+  if (bits > 8) {
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<1024, 1, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)UtCfg<1024>::SMEM));
+    bucket_scatter_tma_kernel<1024, 1, false><<<min(regions * tpr, (uint32_t)ctx->num_sms), 1024,
+                                                UtCfg<1024>::SMEM, st>>>(
+        k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits, cap_seg, cur2, d_flag,
+        hmj_peer_regions(), region_shift);
+  } else {
+    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<512, 2, false>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)UtCfg<512>::SMEM));
+    bucket_scatter_tma_kernel<512, 2, false><<<min(regions * tpr, (uint32_t)ctx->num_sms * 2), 512,
+                                               UtCfg<512>::SMEM, st>>>(
+        k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits, cap_seg, cur2, d_flag,
+        hmj_peer_regions(), region_shift);
+  }
   HMJ_LAUNCHED(ctx);
   hmj_prof_end(ctx, ev);
   return HMJ_OK;

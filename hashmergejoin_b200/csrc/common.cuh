@@ -169,16 +169,17 @@ int hmj_launch_bucket_finish(hmj_ctx* ctx, uint64_t* keys, uint32_t* vals, const
 struct hmj_peer_regions {
   uint64_t* keys[8];
   uint32_t* vals[8];
-  uint32_t* cursors[8];
-  int own_bits;  // log2(regions per GPU)
+  uint32_t* counts[8];  // per owner: pairs in sub-region (region * world + source rank)
+  int own_bits;         // log2(regions per GPU)
+  int world, rank;      // GPUs of the job, this GPU
 };
 int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                             int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
-                            uint32_t* d_flag);
+                            uint32_t* d_cursors, uint32_t* d_flag);
 int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
                        uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
                        uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag);
+                       uint32_t* d_flag, int region_shift);
 struct hmj_uniform_plan {
   int levels;        // 0 = not eligible
   int bits[2];

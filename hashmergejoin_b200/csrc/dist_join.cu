@@ -5,8 +5,9 @@
 // level 1 of the bucket scatter (bucket_scatter.cu) runs over the GPU's local rows with its
 // 2^b1 destination regions spread over the GPUs of the job -- region r belongs to GPU
 // r >> (b1 - log2 G) -- and writes every run straight into the owner's memory through NVLink peer
-// pointers (slot reservation = one system-scope atomicAdd on the owner's cursor).  No partition
-// pass, no send buffers, no NCCL all-to-all; after a barrier every GPU continues locally with
+// pointers.  Every source GPU owns a sub-region of every region (slot reservation = atomicAdd on
+// a cursor in the SOURCE's memory; the counts are handed to the owners after the kernel).  No
+// partition pass, no send buffers, no NCCL all-to-all; after a barrier every GPU continues locally with
 // level 2 and the bucket join on hash bits below the ones that chose the GPU.  It stands in for
 // partition_only's per-thread push_back into shared partitions (partitioned_hash.h:82-124) at
 // the scale of a node.
@@ -21,10 +22,13 @@ struct hmj_dist_state {
   int world = 1, rank = 0;
   int g_bits = 0, b1 = 0, b2 = 0, own_bits = 0;  // level-1 bits (job wide), level-2 bits, log2(own regions)
   uint32_t cap1 = 0, cap_seg = 0, regions_own = 0;
-  // own level-1 regions per side (0 = R, 1 = S): keys, row ids, cursors (+ 8 words: [regions_own] = flag)
+  // own level-1 regions per side (0 = R, 1 = S): regions_own x world sub-regions of cap1 slots
+  // (keys, row ids) and their counts [regions_own * world], all shared with the peers;
   uint64_t* k1[2] = {nullptr, nullptr};
   uint32_t* v1[2] = {nullptr, nullptr};
   uint32_t* c1[2] = {nullptr, nullptr};
+  // private: this source's cursors over all 2^b1 regions of the job (+ 8 words: [2^b1] = flag)
+  uint32_t* cur[2] = {nullptr, nullptr};
   hmj_peer_regions peers[2];
   void* opened[2][8][3] = {};
   size_t rows_total = 0;
@@ -60,15 +64,18 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
   d->b2 = total_bits - d->b1;
   d->own_bits = d->b1 - d->g_bits;
   d->regions_own = 1u << d->own_bits;
-  const double avg1 = (double)rows_total / (double)(1u << d->b1);
+  // a sub-region holds what ONE source sends to a region
+  const double avg1 = (double)rows_total / (double)world / (double)(1u << d->b1);
   d->cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
   d->cap_seg = (uint32_t)hmj_segment_sort_cap();
   for (int s = 0; s < 2; ++s) {
-    const size_t slots = (size_t)d->regions_own * d->cap1;
+    const size_t subs = (size_t)d->regions_own * world;
+    const size_t slots = subs * d->cap1;
     HMJ_CUDA(ctx, cudaMalloc(&d->k1[s], slots * 8));
     HMJ_CUDA(ctx, cudaMalloc(&d->v1[s], slots * 4));
-    HMJ_CUDA(ctx, cudaMalloc(&d->c1[s], ((size_t)d->regions_own + 8) * 4));
-    HMJ_CUDA(ctx, cudaMemset(d->c1[s], 0, ((size_t)d->regions_own + 8) * 4));
+    HMJ_CUDA(ctx, cudaMalloc(&d->c1[s], (subs + 8) * 4));
+    HMJ_CUDA(ctx, cudaMemset(d->c1[s], 0, (subs + 8) * 4));
+    HMJ_CUDA(ctx, cudaMalloc(&d->cur[s], (((size_t)1 << d->b1) + 8) * 4));
     void* ptrs[3] = {d->k1[s], d->v1[s], d->c1[s]};
     for (int j = 0; j < 3; ++j) {
       cudaIpcMemHandle_t h;
@@ -89,6 +96,8 @@ extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) 
   for (int s = 0; s < 2; ++s) {
     memset(&d->peers[s], 0, sizeof d->peers[s]);
     d->peers[s].own_bits = d->own_bits;
+    d->peers[s].world = d->world;
+    d->peers[s].rank = d->rank;
     for (int r = 0; r < d->world; ++r) {
       void* ptrs[3];
       if (r == d->rank) {
@@ -103,22 +112,21 @@ extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) 
       }
       d->peers[s].keys[r] = reinterpret_cast<uint64_t*>(ptrs[0]);
       d->peers[s].vals[r] = reinterpret_cast<uint32_t*>(ptrs[1]);
-      d->peers[s].cursors[r] = reinterpret_cast<uint32_t*>(ptrs[2]);
+      d->peers[s].counts[r] = reinterpret_cast<uint32_t*>(ptrs[2]);
     }
   }
   return HMJ_OK;
 }
 
-// Zeroes this rank's cursors and flags.  Every rank must have done so (and synchronised) before
-// any rank scatters: the caller puts a barrier after it.
+// Zeroes this rank's cursors and flags (private to the rank: no barrier is needed before the
+// scatter; the one after it publishes runs and counts to their owners).
 extern "C" int hmj_dist_begin(hmj_ctx* ctx) {
   if (!ctx) return HMJ_EARG;
   HMJ_ARG(ctx, ctx->dist != nullptr);
   hmj_dist_state* d = ctx->dist;
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   for (int s = 0; s < 2; ++s)
-    HMJ_CUDA(ctx, cudaMemsetAsync(d->c1[s], 0, ((size_t)d->regions_own + 8) * 4, ctx->stream));
-  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    HMJ_CUDA(ctx, cudaMemsetAsync(d->cur[s], 0, (((size_t)1 << d->b1) + 8) * 4, ctx->stream));
   return HMJ_OK;
 }
 
@@ -131,9 +139,9 @@ extern "C" int hmj_dist_scatter(hmj_ctx* ctx, int side, const uint64_t* d_keys, 
   HMJ_ARG(ctx, ctx->dist != nullptr && (side == 0 || side == 1) && (n == 0 || d_keys));
   hmj_dist_state* d = ctx->dist;
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
-  uint32_t* flag = d->c1[side] + d->regions_own;
+  uint32_t* flag = d->cur[side] + ((size_t)1 << d->b1);
   HMJ_TRY(hmj_scatter_level1_dist(ctx, d_keys, n, rowid_base, 64 - d->b1, d->b1, d->cap1,
-                                  d->peers[side], flag));
+                                  d->peers[side], d->cur[side], flag));
   HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return HMJ_OK;
 }
@@ -160,9 +168,10 @@ extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
     const size_t slots2 = (size_t)buckets * d->cap_seg;
     HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, slots2, &k2));
     HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, slots2, &v2));
-    uint32_t* flag = d->c1[s] + d->regions_own;  // level-1 overflows of this rank's regions land here too
-    HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, d->regions_own, n_hint,
-                               64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag));
+    uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);  // this rank's level-1 overflows land here too
+    HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1,
+                               d->regions_own * (uint32_t)d->world, n_hint, 64 - d->b1 - d->b2,
+                               d->b2, k2, v2, d->cap_seg, words + 8, flag, d->g_bits));
     B[s].keys = k2;
     B[s].vals = v2;
     B[s].counts = words + 8;
@@ -187,6 +196,7 @@ extern "C" int hmj_dist_teardown(hmj_ctx* ctx) {
     if (d->k1[s]) cudaFree(d->k1[s]);
     if (d->v1[s]) cudaFree(d->v1[s]);
     if (d->c1[s]) cudaFree(d->c1[s]);
+    if (d->cur[s]) cudaFree(d->cur[s]);
   }
   delete d;
   ctx->dist = nullptr;
