@@ -26,8 +26,6 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-# rank 0 prints ONE JSON line on stdout: NCCL's own banner ("NCCL version ...") goes to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 METRIC = "joined input tuples/sec (build+probe)"
 UNIT = "tuples/s"
@@ -167,7 +165,7 @@ def run_reference(args):
         "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print_line(line)
 
 
 # ------------------------------------------------------------------------------------------
@@ -366,9 +364,21 @@ def run_gpu(args):
         if world > 1:
             line["nvlink"] = {"exchange_bytes_sent_rank0_per_step": joiner.exchange_bytes,
                               "note": "12 B per pair leaving the rank, both relations"}
-        print(json.dumps(line), flush=True)
+        print_line(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def print_line(line):
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+    if _REAL_STDOUT is not None:
+        os.dup2(2, 1)
 
 
 def main():
@@ -381,6 +391,12 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: while the run lasts, file descriptor 1 points at stderr
+    # (NCCL prints its "NCCL version ..." banner on stdout from native code), print_line restores it
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
