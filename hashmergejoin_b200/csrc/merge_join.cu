@@ -713,12 +713,56 @@ int join_fused(hmj_ctx* ctx, JoinPlan* plan, uint32_t* d_out_r, uint32_t* d_out_
   return HMJ_OK;
 }
 
+
+// Samples a sorted hash column for equal-hash runs longer than RUN_PROBE rows: one thread per
+// RUN_PROBE/2 rows compares h[i] with h[i+RUN_PROBE]; the hit count measures how many rows sit
+// in such runs (every run of 1.5*RUN_PROBE rows or more is seen).
+constexpr uint32_t RUN_PROBE = 4096;
+__global__ void run_mass_kernel(const uint64_t* __restrict__ h, uint32_t n, unsigned long long* hits) {
+  const uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * (RUN_PROBE / 2);
+  const bool hit = i + RUN_PROBE < n && h[i] == h[i + RUN_PROBE];
+  const unsigned b = __ballot_sync(0xffffffffu, hit);
+  if ((threadIdx.x & 31) == 0 && b) atomicAdd(hits, (unsigned long long)__popc(b));
+}
+
+// The tile kernel walks, for every row of its first relation, that row's equal-hash run in the
+// second one; a run is walked by one CTA, so the longest run of the second relation is the
+// critical path.  Decide which relation goes second: the one with less mass in long runs.
+int join_wants_swap(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s, bool* swap) {
+  *swap = false;
+  if (r->n <= RUN_PROBE && s->n <= RUN_PROBE) return HMJ_OK;
+  uint64_t* scal = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_SCALARS, 8, &scal));
+  unsigned long long* hits = reinterpret_cast<unsigned long long*>(scal + 4);
+  HMJ_CUDA(ctx, cudaMemsetAsync(hits, 0, 16, ctx->stream));
+  const hmj_relation* rel[2] = {r, s};
+  for (int k = 0; k < 2; ++k) {
+    if (rel[k]->n <= RUN_PROBE) continue;
+    const uint32_t samples = (uint32_t)hmj_div_up(rel[k]->n, RUN_PROBE / 2);
+    run_mass_kernel<<<(samples + 255) / 256, 256, 0, ctx->stream>>>(rel[k]->d_hash, (uint32_t)rel[k]->n, hits + k);
+    HMJ_LAUNCHED(ctx);
+  }
+  uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h, hits, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *swap = h[1] > h[0];
+  return HMJ_OK;
+}
+
 }  // namespace
 
 // whole-operator helper (operator.cu): join two sorted relations into the context's result
-// buffers, growing them when the first (optimistic) capacity was too small.
-int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,
+// buffers, growing them when the first (optimistic) capacity was too small.  The pairs come out
+// in unspecified order: when S holds the long equal-hash runs the relations trade places.
+int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r_in, const hmj_relation* s_in,
                          uint64_t* h_num_pairs) {
+  HMJ_TRY(check_relation(ctx, r_in));
+  HMJ_TRY(check_relation(ctx, s_in));
+  bool swap = false;
+  HMJ_TRY(join_wants_swap(ctx, r_in, s_in, &swap));
+  const hmj_relation* r = swap ? s_in : r_in;
+  const hmj_relation* s = swap ? r_in : s_in;
+  const int slot_r = swap ? WS_OUT_S : WS_OUT_R, slot_s = swap ? WS_OUT_R : WS_OUT_S;
   JoinPlan plan;
   HMJ_TRY(join_plan(ctx, r, s, &plan));
   // optimistic capacity: what the buffers already hold, at least max(|R|,|S|) pairs
@@ -726,15 +770,15 @@ int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation
   const size_t guess = r->n > s->n ? r->n : s->n;
   if (cap < guess) cap = guess;
   uint32_t *out_r = nullptr, *out_s = nullptr;
-  HMJ_TRY(hmj_ws(ctx, WS_OUT_R, cap, &out_r));
-  HMJ_TRY(hmj_ws(ctx, WS_OUT_S, cap, &out_s));
+  HMJ_TRY(hmj_ws(ctx, slot_r, cap, &out_r));
+  HMJ_TRY(hmj_ws(ctx, slot_s, cap, &out_s));
   cap = ctx->ws[WS_OUT_R].bytes / 4;
   if (ctx->ws[WS_OUT_S].bytes / 4 < cap) cap = ctx->ws[WS_OUT_S].bytes / 4;
   uint64_t m = 0;
   HMJ_TRY(join_fused(ctx, &plan, out_r, out_s, cap, &m));
   if (m > cap) {
-    HMJ_TRY(hmj_ws(ctx, WS_OUT_R, (size_t)m, &out_r));
-    HMJ_TRY(hmj_ws(ctx, WS_OUT_S, (size_t)m, &out_s));
+    HMJ_TRY(hmj_ws(ctx, slot_r, (size_t)m, &out_r));
+    HMJ_TRY(hmj_ws(ctx, slot_s, (size_t)m, &out_s));
     uint64_t m2 = 0;
     HMJ_TRY(join_fused(ctx, &plan, out_r, out_s, m, &m2));
     m = m2;

@@ -379,6 +379,31 @@ def test_operator_strings_bucket_join(ctx, oracle):
     assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
 
 
+@pytest.mark.parametrize("skewed_side", ["probe", "build"])
+def test_operator_zipf_relation_trades_places(ctx, oracle, skewed_side):
+    # C5's shape: one relation holds every key twice, the other draws keys Zipf(1.0); the head
+    # keys' runs span many tiles, so the join iterates over the skewed relation whichever side
+    # it is on -- the pairs must not change
+    dkeys = 20000
+    off, chars, _, _ = datagen.strgen(dkeys, seed=21, shuffle_seed=2)
+    rng = np.random.default_rng(6)
+    flat = datagen.take_rows(off, chars, rng.permutation(np.repeat(np.arange(dkeys), 2)))
+    zipf = datagen.take_rows(off, chars, datagen.zipf_indices(150000, dkeys, 1.0, seed=8))
+    (roff, rchars), (soff, schars) = (flat, zipf) if skewed_side == "probe" else (zipf, flat)
+    out_r, out_s = gpu_join_strings(ctx, roff, rchars, soff, schars)
+    assert ctx.timings()["sort_uniform"] != 2, "the bucket join cannot hold a Zipf relation"
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars))
+    assert out_r.size == 300000
+    c_r, c_s = oracle.sort_pairs(out_r, out_s)
+    e_r, e_s = oracle.sort_pairs(t_r, t_s)
+    assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
+    # same with u64 keys (identity hash)
+    ku = datagen.unique_u64(dkeys, seed=3)
+    a = ku[rng.permutation(np.repeat(np.arange(dkeys), 2))]
+    b = ku[datagen.zipf_indices(150000, dkeys, 1.0, seed=9)]
+    check_operator_u64(ctx, oracle, *((a, b) if skewed_side == "probe" else (b, a)))
+
+
 def test_join_golden_duplicates(ctx, oracle):
     g = G.load("dup_join_u64.json")
     rk, sk = G.u64(g["r_keys"]), G.u64(g["s_keys"])
