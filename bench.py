@@ -302,7 +302,52 @@ def run_gpu(args):
         assert chk.all(), "e2e result pairs do not join equal keys"
         e2e = {"value": 2 * rows / dt, "unit": UNIT, "h2d_bytes_per_step": 2 * rows * 8,
                "d2h_bytes_per_step": 2 * rows * 4, "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "api": "hmj_join_u64_host (pinned host buffers)"}
+               "in_flight": 1, "api": "hmj_join_u64_host (pinned host buffers)"}
+        if args.e2e_in_flight > 1:
+            # successive joins from `in_flight` host threads, one context (stream + workspace)
+            # each: a join's D2H of its pairs runs beside the next join's H2D of its keys (PCIe is
+            # full duplex); every join still copies its own inputs in and its own pairs out.
+            import threading
+            lanes = args.e2e_in_flight
+            # a stream of its own per lane (the default Context rides torch's current stream)
+            ctxs = [hmj.Context(local_rank, use_torch_stream=False) for _ in range(lanes)]
+            outs = [(a[2], a[3])]
+            for _ in range(lanes - 1):
+                p_r = torch.empty(rows, dtype=torch.int32).pin_memory()
+                p_s = torch.empty(rows, dtype=torch.int32).pin_memory()
+                outs.append((p_r.numpy().view(np.uint32), p_s.numpy().view(np.uint32)))
+            ctx.close()  # its workspace goes back before the lanes grow theirs
+            for c, (x, y) in zip(ctxs, outs):
+                c.join_u64_host(a[0], a[1], x, y)  # workspace growth
+            per_lane = max(4, e2e_steps)
+            got = [0] * lanes
+
+            def lane(i):
+                # staggered start: joins entering together would queue on the same copy engine
+                # at the same time and leave it together
+                time.sleep(i * dt / lanes)
+                for _ in range(per_lane):
+                    got[i] = ctxs[i].join_u64_host(a[0], a[1], *outs[i])
+
+            th = [threading.Thread(target=lane, args=(i,)) for i in range(lanes)]
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for t in th:
+                t.start()
+            for t in th:
+                t.join()
+            torch.cuda.synchronize()
+            dtp = (time.perf_counter() - t0) / (per_lane * lanes)
+            assert all(g == rows for g in got)
+            for x, y in outs:
+                assert (a[0][x[:1000]] == a[1][y[:1000]]).all(), "pipelined e2e result pairs do not join equal keys"
+            for c in ctxs:
+                c.close()
+            e2e.update({"single_call": {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"]},
+                        "value": 2 * rows / dtp, "ms_per_step": dtp * 1e3, "steps": per_lane * lanes,
+                        "in_flight": lanes,
+                        "api": "hmj_join_u64_host (pinned host buffers), %d joins in flight from %d host "
+                               "threads with a context each; single_call = one join at a time" % (lanes, lanes)})
     elif world > 1 and not args.no_e2e:
         # every rank: pinned host block of both relations -> H2D -> partition / all-to-all /
         # sort / merge join -> D2H of this rank's pairs.  Wall clock between barriers, max over ranks.
@@ -389,6 +434,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-in-flight", type=int, default=2, help="joins in flight in the e2e leg (1 = one at a time)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: while the run lasts, file descriptor 1 points at stderr

@@ -331,7 +331,7 @@ int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
     cap = ctx->ws[WS_OUT_R].bytes / 4;
     if (ctx->ws[WS_OUT_S].bytes / 4 < cap) cap = ctx->ws[WS_OUT_S].bytes / 4;
     A.out_r = out_r; A.out_s = out_s; A.cap = cap;
-    HMJ_CUDA(ctx, cudaMemsetAsync(d_desc, 0, 32, st));
+    HMJ_TRY(hmj_fill_async(ctx, d_desc, 0, 32, st));
     cudaEvent_t ev;
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_BJOIN, ((double)nr + (double)ns) * 12.0, &ev));
     if (kind == HMJ_KEY_U64) {

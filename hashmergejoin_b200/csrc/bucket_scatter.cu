@@ -468,7 +468,7 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
   uint32_t* d_flag = d_words;
   uint32_t* d_cur1 = d_words + 8;
   uint32_t* d_cur2 = p.levels == 2 ? d_cur1 + regions1 : d_cur1;
-  HMJ_CUDA(ctx, cudaMemsetAsync(d_words, 0, (8 + (size_t)regions1 + buckets) * sizeof(uint32_t), st));
+  HMJ_TRY(hmj_fill_async(ctx, d_words, 0, (8 + (size_t)regions1 + buckets) * sizeof(uint32_t), st));
 
   uint64_t *d_k1 = nullptr, *d_k2 = nullptr;
   uint32_t *d_v1 = nullptr, *d_v2 = nullptr;

@@ -116,6 +116,11 @@ static inline int hmj_fail(hmj_ctx* ctx, int code, const char* what, const char*
 
 // returns a device scratch buffer of at least `bytes` bytes in slot `slot`
 int hmj_ws_get(hmj_ctx* ctx, int slot, size_t bytes, void** out);
+// Fill device memory with a byte value by a kernel on `st` (bytes a multiple of 4, ptr 4-byte
+// aligned): control words are cleared on the SMs, in stream order, whatever the copy engines do.
+int hmj_fill_async(hmj_ctx* ctx, void* ptr, int byte, size_t bytes, cudaStream_t st);
+// HMJ_HOST_TRACE=1: wall-clock marks of host-side progress on stderr (debugging aid)
+void hmj_host_mark(hmj_ctx* ctx, const char* what);
 
 template <typename T>
 static inline int hmj_ws(hmj_ctx* ctx, int slot, size_t count, T** out) {

@@ -5,6 +5,9 @@
 
 #include "common.cuh"
 
+#include <chrono>
+#include <cstdlib>
+
 extern "C" const char* hmj_version(void) { return "hmj-b200 0.1 sm_100a"; }
 
 static int hmj_create_impl(hmj_ctx** out, int device, void* stream, bool own) {
@@ -95,6 +98,42 @@ extern "C" int hmj_synchronize(hmj_ctx* ctx) {
 extern "C" int hmj_launch_count(hmj_ctx* ctx, uint64_t* count) {
   if (!ctx || !count) return HMJ_EARG;
   *count = ctx->launches;
+  return HMJ_OK;
+}
+
+namespace {
+__global__ void __launch_bounds__(256) fill_words_kernel(uint32_t* __restrict__ p, uint32_t word, size_t words) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((reinterpret_cast<uintptr_t>(p) & 15) == 0) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    const uint4 v = make_uint4(word, word, word, word);
+    for (size_t k = i; k < words / 4; k += stride) q[k] = v;
+    for (size_t k = (words & ~size_t(3)) + i; k < words; k += stride) p[k] = word;
+  } else {
+    for (; i < words; i += stride) p[i] = word;
+  }
+}
+}  // namespace
+
+void hmj_host_mark(hmj_ctx* ctx, const char* what) {
+  static const bool on = getenv("HMJ_HOST_TRACE") != nullptr;
+  if (!on) return;
+  const double ms = std::chrono::duration<double, std::milli>(
+                        std::chrono::steady_clock::now().time_since_epoch()).count();
+  fprintf(stderr, "[hmj host %p] %.1f %s\n", (void*)ctx, ms, what);
+}
+
+int hmj_fill_async(hmj_ctx* ctx, void* ptr, int byte, size_t bytes, cudaStream_t st) {
+  if (bytes == 0) return HMJ_OK;
+  HMJ_ARG(ctx, ptr != nullptr && (bytes & 3) == 0 && (reinterpret_cast<uintptr_t>(ptr) & 3) == 0);
+  const uint32_t word = 0x01010101u * (uint32_t)(byte & 0xFF);
+  const size_t words = bytes / 4;
+  size_t blocks = (words / 4 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  fill_words_kernel<<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<uint32_t*>(ptr), word, words);
+  HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 

@@ -126,7 +126,7 @@ extern "C" int hmj_dist_begin(hmj_ctx* ctx) {
   hmj_dist_state* d = ctx->dist;
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   for (int s = 0; s < 2; ++s)
-    HMJ_CUDA(ctx, cudaMemsetAsync(d->cur[s], 0, (((size_t)1 << d->b1) + 8) * 4, ctx->stream));
+    HMJ_TRY(hmj_fill_async(ctx, d->cur[s], 0, (((size_t)1 << d->b1) + 8) * 4, ctx->stream));
   return HMJ_OK;
 }
 
@@ -162,7 +162,7 @@ extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
   for (int s = 0; s < 2; ++s) {
     uint32_t* words = nullptr;
     HMJ_TRY(hmj_ws(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, (size_t)buckets + 8, &words));
-    HMJ_CUDA(ctx, cudaMemsetAsync(words, 0, ((size_t)buckets + 8) * 4, st));
+    HMJ_TRY(hmj_fill_async(ctx, words, 0, ((size_t)buckets + 8) * 4, st));
     uint64_t* k2 = nullptr;
     uint32_t* v2 = nullptr;
     const size_t slots2 = (size_t)buckets * d->cap_seg;

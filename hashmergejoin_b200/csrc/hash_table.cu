@@ -162,13 +162,13 @@ extern "C" int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r, con
   HMJ_TRY(hmj_ws(ctx, WS_TABLE, cap, &table));
   // EMPTY hash = all ones, row1 must be 0: two memsets over the interleaved slots would be
   // wasteful, so fill with 0xFF and let row1 use the complement convention instead.
-  HMJ_CUDA(ctx, cudaMemsetAsync(table, 0xFF, cap * sizeof(HtSlot), st));
+  HMJ_TRY(hmj_fill_async(ctx, table, 0xFF, cap * sizeof(HtSlot), st));
   // row1 == 0xFFFFFFFF after the fill; a tiny kernel-free trick is not possible, so reset row1
   // with a strided 2D memset (4 bytes every 16).
   HMJ_CUDA(ctx, cudaMemset2DAsync(reinterpret_cast<char*>(table) + 8, sizeof(HtSlot), 0, 4, cap, st));
   uint64_t* scal = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_SCALARS, 8, &scal));
-  HMJ_CUDA(ctx, cudaMemsetAsync(scal, 0, 16, st));
+  HMJ_TRY(hmj_fill_async(ctx, scal, 0, 16, st));
 
   HtArgs B = {};
   B.table = table; B.mask = cap - 1; B.shift = 64 - log2cap;

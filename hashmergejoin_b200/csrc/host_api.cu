@@ -3,8 +3,34 @@
 // benchmark call; the copies are inside the call on purpose.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace {
 enum { EV_START = 0, EV_HASHED, EV_SORTED, EV_JOINED, EV_H2D, EV_D2H };
+
+// One host thread at a time per GPU and direction on the host link.  Large copies issued from
+// several streams share a copy engine slice by slice, so joins in flight from several host
+// threads (a context each) would all finish their input copies together and then all copy
+// their pairs out together; taking turns lets one join's pairs leave while the next join's
+// keys arrive (the link is full duplex: 45 + 45 GB/s measured against 55 one way).
+std::mutex g_turn[2][64];
+class CopyTurn {
+ public:
+  CopyTurn(hmj_ctx* ctx, int dir) : ctx_(ctx), lock_(g_turn[dir][ctx->device & 63]) {}
+  // the copies issued in this turn have landed
+  int finish() {
+    const cudaError_t e = cudaStreamSynchronize(ctx_->stream);
+    lock_.unlock();
+    HMJ_CUDA(ctx_, e);
+    return HMJ_OK;
+  }
+ private:
+  hmj_ctx* ctx_;
+  std::unique_lock<std::mutex> lock_;
+};
+enum { TURN_H2D = 0, TURN_D2H = 1 };
+
+void mark(hmj_ctx* ctx, const char* what) { hmj_host_mark(ctx, what); }
 
 template <typename T>
 int stage_in(hmj_ctx* ctx, int slot, const T* h_src, size_t count, T** d_dst) {
@@ -28,10 +54,23 @@ extern "C" int hmj_join_u64_host(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t n
   HMJ_ARG(ctx, h_num_pairs && (nr == 0 || h_rkeys) && (ns == 0 || h_skeys));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   uint64_t *dr = nullptr, *ds = nullptr;
-  HMJ_TRY(stage_in(ctx, WS_IN_0, h_rkeys, nr, &dr));
-  HMJ_TRY(stage_in(ctx, WS_IN_1, h_skeys, ns, &ds));
+  mark(ctx, "enter");
+  {
+    CopyTurn turn(ctx, TURN_H2D);
+    mark(ctx, "h2d turn");
+    HMJ_TRY(stage_in(ctx, WS_IN_0, h_rkeys, nr, &dr));
+    HMJ_TRY(stage_in(ctx, WS_IN_1, h_skeys, ns, &ds));
+    HMJ_TRY(turn.finish());
+  }
+  mark(ctx, "h2d done");
   HMJ_TRY(hmj_join_u64(ctx, dr, nr, ds, ns, h_num_pairs));
-  if (h_out_r || h_out_s) HMJ_TRY(hmj_join_result_to_host(ctx, h_out_r, h_out_s, cap));
+  mark(ctx, "joined");
+  if (h_out_r || h_out_s) {
+    CopyTurn turn(ctx, TURN_D2H);
+    mark(ctx, "d2h turn");
+    HMJ_TRY(hmj_join_result_to_host(ctx, h_out_r, h_out_s, cap));
+  }
+  mark(ctx, "leave");
   return HMJ_OK;
 }
 
@@ -45,12 +84,19 @@ extern "C" int hmj_join_strings_host(hmj_ctx* ctx, const uint64_t* h_roffsets,
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   uint64_t *dro = nullptr, *dso = nullptr;
   uint8_t *drc = nullptr, *dsc = nullptr;
-  HMJ_TRY(stage_in(ctx, WS_IN_0, h_roffsets, nr + 1, &dro));
-  HMJ_TRY(stage_in(ctx, WS_IN_1, h_rchars, (size_t)h_roffsets[nr], &drc));
-  HMJ_TRY(stage_in(ctx, WS_IN_2, h_soffsets, ns + 1, &dso));
-  HMJ_TRY(stage_in(ctx, WS_IN_3, h_schars, (size_t)h_soffsets[ns], &dsc));
+  {
+    CopyTurn turn(ctx, TURN_H2D);
+    HMJ_TRY(stage_in(ctx, WS_IN_0, h_roffsets, nr + 1, &dro));
+    HMJ_TRY(stage_in(ctx, WS_IN_1, h_rchars, (size_t)h_roffsets[nr], &drc));
+    HMJ_TRY(stage_in(ctx, WS_IN_2, h_soffsets, ns + 1, &dso));
+    HMJ_TRY(stage_in(ctx, WS_IN_3, h_schars, (size_t)h_soffsets[ns], &dsc));
+    HMJ_TRY(turn.finish());
+  }
   HMJ_TRY(hmj_join_strings(ctx, dro, drc, nr, dso, dsc, ns, h_num_pairs));
-  if (h_out_r || h_out_s) HMJ_TRY(hmj_join_result_to_host(ctx, h_out_r, h_out_s, cap));
+  if (h_out_r || h_out_s) {
+    CopyTurn turn(ctx, TURN_D2H);
+    HMJ_TRY(hmj_join_result_to_host(ctx, h_out_r, h_out_s, cap));
+  }
   return HMJ_OK;
 }
 

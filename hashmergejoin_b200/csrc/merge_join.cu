@@ -702,7 +702,7 @@ int join_fused(hmj_ctx* ctx, JoinPlan* plan, uint32_t* d_out_r, uint32_t* d_out_
   A.out_r = d_out_r;
   A.out_s = d_out_s;
   A.cap = cap;
-  HMJ_CUDA(ctx, cudaMemsetAsync(A.tile_desc, 0, (size_t)A.tiles * 8 + 16, ctx->stream));
+  HMJ_TRY(hmj_fill_async(ctx, A.tile_desc, 0, (size_t)A.tiles * 8 + 16, ctx->stream));
   HMJ_TRY(launch_tiles<JOIN_FUSED>(ctx, *plan));
   uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
   HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.agg + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -734,7 +734,7 @@ int join_wants_swap(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s, 
   uint64_t* scal = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_SCALARS, 8, &scal));
   unsigned long long* hits = reinterpret_cast<unsigned long long*>(scal + 4);
-  HMJ_CUDA(ctx, cudaMemsetAsync(hits, 0, 16, ctx->stream));
+  HMJ_TRY(hmj_fill_async(ctx, hits, 0, 16, ctx->stream));
   const hmj_relation* rel[2] = {r, s};
   for (int k = 0; k < 2; ++k) {
     if (rel[k]->n <= RUN_PROBE) continue;
@@ -824,7 +824,7 @@ extern "C" int hmj_merge_join_aggregate(hmj_ctx* ctx, const hmj_relation* r,
   if (plan.args.tiles == 0) return HMJ_OK;
   plan.args.rvals = d_rvals;
   plan.args.svals = d_svals;
-  HMJ_CUDA(ctx, cudaMemsetAsync(plan.args.agg, 0, 16, ctx->stream));
+  HMJ_TRY(hmj_fill_async(ctx, plan.args.agg, 0, 16, ctx->stream));
   HMJ_TRY(launch_tiles<JOIN_AGG>(ctx, plan));
   uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
   HMJ_CUDA(ctx, cudaMemcpyAsync(h, plan.args.agg, 16, cudaMemcpyDeviceToHost, ctx->stream));

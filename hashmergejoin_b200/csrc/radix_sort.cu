@@ -596,7 +596,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   uint32_t* d_stats = d_hist + NUM_PASSES * RADIX;
   uint32_t* d_counters = d_stats + 2 * NUM_PASSES;
   uint32_t* d_flag = d_counters + MAX_LAUNCHED_PASSES;
-  HMJ_CUDA(ctx, cudaMemsetAsync(d_hist, 0, hist_words * sizeof(uint32_t), st));
+  HMJ_TRY(hmj_fill_async(ctx, d_hist, 0, hist_words * sizeof(uint32_t), st));
 
   const size_t chunk = (size_t)HIST_THREADS * HIST_ITEMS;
   const int hgrid = (int)min(hmj_div_up(n, chunk), (size_t)ctx->num_sms * 4);
@@ -721,7 +721,7 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
     HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, tiles * RADIX, &d_lb));
     if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
         ctx->lb_epoch + 3 * NUM_PASSES >= 0xFFFF) {
-      HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
+      HMJ_TRY(hmj_fill_async(ctx, d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
       ctx->lb_seen_ptr = d_lb;
       ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
       ctx->lb_epoch = 0;
@@ -914,7 +914,7 @@ extern "C" int hmj_partition_counts(hmj_ctx* ctx, const uint64_t* d_hash, size_t
   HMJ_ARG(ctx, bits >= 1 && bits <= 16 && d_counts && (n == 0 || d_hash));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   const int bins = 1 << bits;
-  HMJ_CUDA(ctx, cudaMemsetAsync(d_counts, 0, (size_t)bins * 8, ctx->stream));
+  HMJ_TRY(hmj_fill_async(ctx, d_counts, 0, (size_t)bins * 8, ctx->stream));
   if (n == 0) return HMJ_OK;
   const int use_smem = bits <= 12;
   const int grid = (int)min(hmj_div_up(n, PART_THREADS * 8), (size_t)ctx->num_sms * 4);
@@ -949,7 +949,7 @@ extern "C" int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash,
   HMJ_TRY(hmj_ws(ctx, WS_HIST, hist_words, &d_hist));
   uint32_t* d_skip = d_hist + NUM_PASSES * RADIX;
   uint32_t* d_counters = d_skip + NUM_PASSES;
-  HMJ_CUDA(ctx, cudaMemsetAsync(d_hist, 0, hist_words * sizeof(uint32_t), st));
+  HMJ_TRY(hmj_fill_async(ctx, d_hist, 0, hist_words * sizeof(uint32_t), st));
   if (n) {
     const int grid = (int)min(hmj_div_up(n, PART_THREADS * 8), (size_t)ctx->num_sms * 4);
     partition_count_kernel<uint32_t><<<grid, PART_THREADS, RADIX * 4, st>>>(d_hash, n, 64 - bits, RADIX, d_hist, 1);
@@ -966,7 +966,7 @@ extern "C" int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash,
   HMJ_TRY(hmj_ws(ctx, WS_LOOKBACK, tiles * RADIX, &d_lb));
   if (ctx->lb_seen_ptr != d_lb || ctx->lb_seen_bytes != ctx->ws[WS_LOOKBACK].bytes ||
       ctx->lb_epoch + NUM_PASSES >= 0xFFFF) {
-    HMJ_CUDA(ctx, cudaMemsetAsync(d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
+    HMJ_TRY(hmj_fill_async(ctx, d_lb, 0, ctx->ws[WS_LOOKBACK].bytes, st));
     ctx->lb_seen_ptr = d_lb;
     ctx->lb_seen_bytes = ctx->ws[WS_LOOKBACK].bytes;
     ctx->lb_epoch = 0;
