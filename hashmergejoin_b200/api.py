@@ -178,6 +178,12 @@ class Context:
         self._ck(self.lib.hmj_join_result(self.h, C.byref(pr), C.byref(ps), C.byref(m)))
         return pr.value, ps.value, m.value
 
+    def join_result_tensors(self, m):
+        """the last whole-operator result as two int32 CUDA tensors (hmj_join_result_copy)"""
+        out_r, out_s = self._empty(m, self._torch.int32), self._empty(m, self._torch.int32)
+        self._ck(self.lib.hmj_join_result_copy(self.h, _dptr(out_r), _dptr(out_s), m))
+        return out_r, out_s
+
     # ---- multi-GPU join, exchange fused into the first scatter level (dist_join.cu)
     def dist_setup(self, rank, world, rows_total):
         handles = np.zeros(6 * 64, np.uint8)
@@ -200,11 +206,29 @@ class Context:
         self._ck(self.lib.hmj_dist_join(self.h, C.byref(m), C.byref(ok)))
         return m.value, ok.value
 
-    def join_strings(self, roff, rchars, soff, schars):
+    def join_strings(self, roff, rchars, soff, schars, prefix_bits=0):
+        """hmj_join_strings[_range]: prefix_bits > 0 when every key hashes into one hash range
+        (the local step of the multi-GPU join)"""
         m = C.c_uint64()
-        self._ck(self.lib.hmj_join_strings(self.h, _dptr(roff), _dptr(rchars), roff.numel() - 1,
-                                           _dptr(soff), _dptr(schars), soff.numel() - 1, C.byref(m)))
+        self._ck(self.lib.hmj_join_strings_range(self.h, _dptr(roff), _dptr(rchars), roff.numel() - 1,
+                                                 _dptr(soff), _dptr(schars), soff.numel() - 1,
+                                                 prefix_bits, C.byref(m)))
         return m.value
+
+    def gather_strings(self, offsets, chars, rows):
+        """keys of `rows` (int32 tensor of row ids) as a new (offsets, chars) column pair"""
+        t = self._torch
+        _check_dev(offsets, 8)
+        n = rows.numel()
+        idx = rows.to(t.int64)
+        out_off = t.zeros(n + 1, dtype=t.int64, device=offsets.device)
+        if n:
+            t.cumsum(offsets[idx + 1] - offsets[idx], 0, out=out_off[1:])
+        total = int(out_off[-1].item()) if n else 0
+        out_chars = self._empty(max(total, 1), t.uint8)[:total]
+        self._ck(self.lib.hmj_gather_strings(self.h, _dptr(offsets), _dptr(chars), _dptr(rows), n,
+                                             _dptr(out_off), _dptr(out_chars)))
+        return out_off, out_chars
 
     def join_result_to_host(self, m):
         out_r = np.empty(m, dtype=np.uint32)

@@ -103,8 +103,14 @@ extern "C" int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint3
 extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
                                 size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars,
                                 size_t ns, uint64_t* h_num_pairs) {
+  return hmj_join_strings_range(ctx, d_roffsets, d_rchars, nr, d_soffsets, d_schars, ns, 0, h_num_pairs);
+}
+
+extern "C" int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
+                                      size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars,
+                                      size_t ns, int prefix_bits, uint64_t* h_num_pairs) {
   if (!ctx) return HMJ_EARG;
-  HMJ_ARG(ctx, h_num_pairs != nullptr);
+  HMJ_ARG(ctx, h_num_pairs != nullptr && prefix_bits >= 0 && prefix_bits <= 16);
   HMJ_ARG(ctx, (nr == 0 || d_roffsets) && (ns == 0 || d_soffsets));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->tm.sort_passes = 0;
@@ -126,7 +132,7 @@ extern "C" int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const 
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
   {
     int ok = 0;
-    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nullptr, nr, st, nullptr, ns, 0, d_roffsets, d_rchars,
+    HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nullptr, nr, st, nullptr, ns, prefix_bits, d_roffsets, d_rchars,
                                  d_soffsets, d_schars, ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
       ctx->tm.sort_uniform += 2;
@@ -163,6 +169,17 @@ extern "C" int hmj_join_result_to_host(hmj_ctx* ctx, uint32_t* h_out_r, uint32_t
   HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_r, ctx->ws[WS_OUT_R].ptr, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
   HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_s, ctx->ws[WS_OUT_S].ptr, m * 4, cudaMemcpyDeviceToHost, ctx->stream));
   HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return HMJ_OK;
+}
+
+extern "C" int hmj_join_result_copy(hmj_ctx* ctx, uint32_t* d_out_r, uint32_t* d_out_s, size_t cap) {
+  if (!ctx) return HMJ_EARG;
+  const size_t m = (size_t)ctx->last_pairs;
+  if (m > cap) return hmj_fail(ctx, HMJ_ECAPACITY, "output capacity too small", __FILE__, __LINE__);
+  if (m == 0) return HMJ_OK;
+  HMJ_ARG(ctx, d_out_r && d_out_s);
+  HMJ_CUDA(ctx, cudaMemcpyAsync(d_out_r, ctx->ws[WS_OUT_R].ptr, m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+  HMJ_CUDA(ctx, cudaMemcpyAsync(d_out_s, ctx->ws[WS_OUT_S].ptr, m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
   return HMJ_OK;
 }
 

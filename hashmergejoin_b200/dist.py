@@ -51,6 +51,41 @@ def exchange_pairs(part_hash, part_rowid, part_offsets, rank, world, group=None)
     return rh, rr, mat
 
 
+def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, world, group=None):
+    """The exchange step for string keys: the keys travel with their rows.
+    part_rowid: this rank's global row ids grouped by destination (bucket g at
+    [part_offsets[g], part_offsets[g+1])); key_offsets/key_chars: the keys in that same order.
+    Returns (rowid, offsets, chars) of everything destined to this rank, source-rank-major, and
+    the bytes this rank sent to other ranks.  The hashes stay behind: the receiver hashes the
+    keys again (8 bytes per row less on the wire).  Works on whatever device the tensors are on."""
+    dev = part_rowid.device
+    po = part_offsets[:world + 1].to(torch.int64)
+    rows = (po[1:] - po[:-1]).contiguous()
+    ko = key_offsets.to(torch.int64)
+    nbytes = (ko[po[1:]] - ko[po[:-1]]).contiguous()
+    mine = torch.cat([rows, nbytes])
+    allc = torch.empty(world * 2 * world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(allc, mine, group=group)
+    allc = allc.view(world, 2, world).cpu()
+    row_mat, byte_mat = allc[:, 0, :].tolist(), allc[:, 1, :].tolist()
+    send_rows, recv_rows = plan_exchange(row_mat, rank)
+    send_bytes, recv_bytes = plan_exchange(byte_mat, rank)
+    assert sum(send_rows) == part_rowid.numel() and sum(send_bytes) == key_chars.numel(), \
+        "partition offsets do not cover the local rows"
+    lens = (ko[1:] - ko[:-1]).to(torch.int32).contiguous()
+    r_rowid = torch.empty(sum(recv_rows), dtype=part_rowid.dtype, device=dev)
+    r_lens = torch.empty(sum(recv_rows), dtype=torch.int32, device=dev)
+    r_chars = torch.empty(sum(recv_bytes), dtype=key_chars.dtype, device=dev)
+    dist.all_to_all_single(r_rowid, part_rowid.contiguous(), recv_rows, send_rows, group=group)
+    dist.all_to_all_single(r_lens, lens, recv_rows, send_rows, group=group)
+    dist.all_to_all_single(r_chars, key_chars.contiguous(), recv_bytes, send_bytes, group=group)
+    r_off = torch.zeros(r_lens.numel() + 1, dtype=torch.int64, device=dev)
+    if r_lens.numel():
+        torch.cumsum(r_lens.to(torch.int64), 0, out=r_off[1:])
+    sent = 8 * (sum(send_rows) - send_rows[rank]) + sum(send_bytes) - send_bytes[rank]
+    return r_rowid, r_off, r_chars, sent
+
+
 class DistJoin:
     def __init__(self, ctx, rank, world, rows_total_hint=0):
         self.ctx, self.rank, self.world = ctx, rank, world
@@ -120,3 +155,36 @@ class DistJoin:
             return out_r.numel(), (out_r, out_s, rh, sh)
         # the rank's hash range shares its top log2(G) bits: bucket join below them
         return ctx.join_pairs(rh, rr, sh, sr, prefix_bits=self.bits)
+
+    def _exchange_side_strings(self, offsets, chars, rowid_base):
+        """hash local keys, group rows by destination, put the keys in send order, exchange ->
+        (global row ids, offsets, chars) of my hash range"""
+        ctx, G = self.ctx, self.world
+        n = offsets.numel() - 1
+        if G == 1:
+            rid = torch.arange(rowid_base, rowid_base + n, dtype=torch.int64, device=offsets.device).to(torch.int32)
+            return rid, offsets, chars
+        h = ctx.hash_strings(offsets, chars)
+        _, rows, offs = ctx.partition_pairs(h, None, self.bits, rowid_base=0)   # local row ids by destination
+        k_off, k_chars = ctx.gather_strings(offsets, chars, rows)
+        rid, r_off, r_chars, sent = exchange_strings(rows + rowid_base, offs, k_off, k_chars, self.rank, G)
+        self.exchange_bytes += sent
+        return rid, r_off, r_chars
+
+    def join_strings(self, roff_local, rchars_local, soff_local, schars_local, want_pairs=False):
+        """String-key join over the ranks (C5's shape).  Each rank passes its block of both
+        relations as offsets[n+1] + chars; global row ids are rank-major blocks as in join_u64.
+        Returns the number of pairs of this rank's hash range, and with want_pairs the pairs as
+        global (build row, probe row) tensors."""
+        ctx = self.ctx
+        nr, ns = roff_local.numel() - 1, soff_local.numel() - 1
+        self.exchange_bytes = 0
+        r_id, r_off, r_chars = self._exchange_side_strings(roff_local, rchars_local, self.rank * nr)
+        s_id, s_off, s_chars = self._exchange_side_strings(soff_local, schars_local, self.rank * ns)
+        self.local_rows = (r_id.numel(), s_id.numel())
+        # received keys are indexed by arrival position; the join reports positions
+        m = ctx.join_strings(r_off, r_chars, s_off, s_chars, prefix_bits=self.bits)
+        if not want_pairs:
+            return m
+        out_r, out_s = ctx.join_result_tensors(m)
+        return m, (r_id[out_r.to(torch.int64)], s_id[out_s.to(torch.int64)])

@@ -134,11 +134,27 @@ int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint32_t* d_rrow
 int hmj_join_strings(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
                      size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars, size_t ns,
                      uint64_t* h_num_pairs);
+/* hmj_join_strings on one hash range: every key's std::hash shares its topmost `prefix_bits` bits
+ * (the rank's range after the hash-range exchange of the multi-GPU join, partitioned_hash.h:59
+ * h >> (64 - bits)).  The bucket plan skips those bits; results are the same as with 0. */
+int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8_t* d_rchars,
+                           size_t nr, const uint64_t* d_soffsets, const uint8_t* d_schars,
+                           size_t ns, int prefix_bits, uint64_t* h_num_pairs);
+/* Copies the keys of rows d_rows[0..n) into a new column pair in that order: d_out_offsets[n+1]
+ * is given (exclusive prefix sum of the rows' lengths), d_out_chars receives the bytes.  The
+ * string side of partition_only's row movement (partitioned_hash.h:102-110): keys are put in
+ * send order once, before the hash-range exchange. */
+int hmj_gather_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const uint8_t* d_chars,
+                       const uint32_t* d_rows, size_t n, const uint64_t* d_out_offsets,
+                       uint8_t* d_out_chars);
 /* device pointers to the last join's pairs (valid until the next join / destroy). */
 int hmj_join_result(hmj_ctx* ctx, const uint32_t** d_out_r, const uint32_t** d_out_s,
                     uint64_t* num_pairs);
 /* copies the last join's pairs to host arrays of capacity cap. */
 int hmj_join_result_to_host(hmj_ctx* ctx, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap);
+/* Same, into caller-owned device buffers (stream-ordered, not synchronised): for callers that
+ * keep working on the device, e.g. the multi-GPU join mapping arrival positions to global rows. */
+int hmj_join_result_copy(hmj_ctx* ctx, uint32_t* d_out_r, uint32_t* d_out_s, size_t cap);
 
 /* Same operator with HOST buffers: H2D copies, join and D2H of the pairs inside the call.
  * This is what the C++ facade and the e2e benchmark call. h_out_* may be NULL (count only). */

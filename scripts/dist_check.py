@@ -66,6 +66,31 @@ def main():
                   f"fused_joins={joiner.fused_joins} pairs={a.size} expected={e_r.size} "
                   f"{'OK' if ok else 'MISMATCH'}", flush=True)
             assert ok
+    # string keys (C5's shape): build side every key twice, probe side Zipf(1.0); keys travel with
+    # their rows over NCCL, the local join verifies them
+    n_keys = max(rows_total // 16, 1024)
+    off, chars, _, _ = datagen.strgen(n_keys, seed=31, shuffle_seed=3)
+    rng = np.random.default_rng(17)
+    r_rows = rng.permutation(np.repeat(np.arange(n_keys), 2))
+    s_rows = datagen.zipf_indices(2 * n_keys, n_keys, 1.0, seed=5)
+    n = 2 * n_keys // world
+    devb = lambda a: torch.from_numpy(a.view({8: np.int64, 1: np.uint8}[a.dtype.itemsize])).cuda()
+    blk = [datagen.take_rows(off, chars, rows[rank * n:(rank + 1) * n]) for rows in (r_rows, s_rows)]
+    joiner = DistJoin(ctx, rank, world)
+    m, (g_r, g_s) = joiner.join_strings(devb(blk[0][0]), devb(blk[0][1]), devb(blk[1][0]), devb(blk[1][1]),
+                                        want_pairs=True)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (g_r.cpu().numpy().view(np.uint32), g_s.cpu().numpy().view(np.uint32),
+                                      joiner.local_rows, joiner.exchange_bytes))
+    if rank == 0:
+        a = np.concatenate([g[0] for g in gathered])
+        b = np.concatenate([g[1] for g in gathered])
+        e_r, e_s = expected_pairs(r_rows.astype(np.uint64), s_rows.astype(np.uint64))  # equal dictionary row = equal key
+        ok = all(np.array_equal(x, y) for x, y in zip(canon(a, b), canon(e_r, e_s)))
+        print(f"world {world} strings: {2 * n_keys} x {2 * n_keys} rows, pairs={a.size} expected={e_r.size} "
+              f"rows per rank {[g[2] for g in gathered]} bytes sent {[g[3] for g in gathered]} "
+              f"{'OK' if ok else 'MISMATCH'}", flush=True)
+        assert ok
     dist.barrier()
     ctx.close()
     dist.destroy_process_group()

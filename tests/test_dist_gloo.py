@@ -18,7 +18,7 @@ import torch.distributed as dist  # noqa: E402
 import torch.multiprocessing as mp  # noqa: E402
 
 from hashmergejoin_b200 import datagen  # noqa: E402
-from hashmergejoin_b200.dist import exchange_pairs, partition_bits, plan_exchange  # noqa: E402
+from hashmergejoin_b200.dist import exchange_pairs, exchange_strings, partition_bits, plan_exchange  # noqa: E402
 
 
 def _free_port():
@@ -101,6 +101,67 @@ def test_dist_join_host_logic_gloo(tmp_path, oracle, world, dup):
     c_r, c_s = oracle.sort_pairs(g_r, g_s)
     assert c_r.size == n_total * dup
     assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+
+
+def make_string_relations(n_keys):
+    """C5's shape in small: build side holds every key twice, probe side draws keys Zipf(1.0)"""
+    off, chars, _, _ = datagen.strgen(n_keys, seed=31, shuffle_seed=3)
+    rng = np.random.default_rng(17)
+    r = datagen.take_rows(off, chars, rng.permutation(np.repeat(np.arange(n_keys), 2)))
+    s = datagen.take_rows(off, chars, datagen.zipf_indices(2 * n_keys, n_keys, 1.0, seed=5))
+    return r, s
+
+
+def _string_worker(rank, world, port, n_keys, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import sys
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        from tests.oracle_binding import Keys, load_oracle
+        oracle = load_oracle()
+        bits = partition_bits(world)
+        rel = make_string_relations(n_keys)
+        n = 2 * n_keys // world
+        got = {}
+        for name, (off, chars) in zip("rs", rel):
+            m_off, m_chars = datagen.take_rows(off, chars, np.arange(rank * n, (rank + 1) * n))
+            # what the device does before the exchange: hash, group rows by destination (stable),
+            # put the keys in that order
+            h = oracle.hash_strings(m_off, m_chars)
+            _, rows, offs = host_partition(h, 0, bits)
+            k_off, k_chars = datagen.take_rows(m_off, m_chars, rows.astype(np.int64))
+            t = torch.from_numpy
+            rid, r_off, r_chars, sent = exchange_strings(
+                t((rows + np.uint32(rank * n)).view(np.int32).copy()), t(offs), t(k_off.view(np.int64).copy()),
+                t(k_chars.copy()), rank, world)
+            r_off, r_chars = r_off.numpy().view(np.uint64), r_chars.numpy()
+            assert r_off[-1] == r_chars.size and sent > 0
+            hh = oracle.hash_strings(r_off, r_chars)
+            assert np.all((hh >> np.uint64(64 - bits)) == rank), "received a key of another hash range"
+            got[name] = (rid.numpy().view(np.uint32), r_off, r_chars)
+        (r_id, r_off, r_chars), (s_id, s_off, s_chars) = got["r"], got["s"]
+        # local join of my range on arrival positions, then positions -> global rows
+        t_r, t_s, _ = oracle.full_join(Keys(offsets=r_off, chars=r_chars), Keys(offsets=s_off, chars=s_chars))
+        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), out_r=r_id[t_r], out_s=s_id[t_s])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_dist_string_join_host_logic_gloo(tmp_path, oracle, world):
+    from tests.oracle_binding import Keys
+    n_keys = 3000
+    mp.spawn(_string_worker, args=(world, _free_port(), n_keys, str(tmp_path)), nprocs=world, join=True)
+    (roff, rchars), (soff, schars) = make_string_relations(n_keys)
+    parts = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars))
+    c_r, c_s = oracle.sort_pairs(np.concatenate([p["out_r"] for p in parts]),
+                                 np.concatenate([p["out_s"] for p in parts]))
+    e_r, e_s = oracle.sort_pairs(t_r, t_s)
+    assert c_r.size == 4 * n_keys
+    assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
 
 
 def test_plan_exchange_and_bits():

@@ -446,6 +446,37 @@ def gpu_join_strings(ctx, off, chars, off2, chars2):
     return ctx.join_result_to_host(m)
 
 
+def test_gather_strings_puts_keys_in_row_order(ctx):
+    off, chars, _, _ = datagen.strgen(70000, seed=19, shuffle_seed=4)
+    rng = np.random.default_rng(2)
+    for rows in (rng.integers(0, 70000, size=100001), np.arange(70000)[::-1].copy(), np.empty(0, np.int64)):
+        g_off, g_chars = ctx.gather_strings(dev(off), dev(chars), dev(rows.astype(np.uint32)))
+        e_off, e_chars = datagen.take_rows(off, chars, rows)
+        assert np.array_equal(g_off.cpu().numpy().view(np.uint64), e_off)
+        assert np.array_equal(g_chars.cpu().numpy(), e_chars)
+
+
+def test_join_strings_of_one_hash_range(ctx, oracle):
+    # the local step of the multi-GPU string join: every key's std::hash has the same top 2 bits
+    off, chars, _, _ = datagen.strgen(400000, seed=23, shuffle_seed=5)
+    h = oracle.hash_strings(off, chars)
+    mine = np.flatnonzero((h >> np.uint64(62)) == 1)
+    rng = np.random.default_rng(8)
+    roff, rchars = datagen.take_rows(off, chars, rng.permutation(np.concatenate([mine, mine[:5000]])))
+    soff, schars = datagen.take_rows(off, chars, rng.permutation(mine)[: mine.size * 3 // 4])
+    t_r, t_s, _ = oracle.full_join(Keys(offsets=roff, chars=rchars), Keys(offsets=soff, chars=schars))
+    e_r, e_s = oracle.sort_pairs(t_r, t_s)
+    for bits, uniform in ((2, True), (0, False)):
+        m = ctx.join_strings(dev(roff), dev(rchars), dev(soff), dev(schars), prefix_bits=bits)
+        assert (ctx.timings()["sort_uniform"] == 2) == uniform
+        c_r, c_s = oracle.sort_pairs(*ctx.join_result_to_host(m))
+        assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
+        # the device-side copy of the result is the same list
+        d_r, d_s = ctx.join_result_tensors(m)
+        c_r, c_s = oracle.sort_pairs(d_r.cpu().numpy().view(np.uint32), d_s.cpu().numpy().view(np.uint32))
+        assert np.array_equal(c_r, e_r) and np.array_equal(c_s, e_s)
+
+
 def test_join_strings_golden(ctx, oracle):
     g = G.load("strgen_join_600.json")
     off, chars = np.array(g["r_offsets"], np.uint64), G.u8(g["r_chars_hex"])
