@@ -349,8 +349,8 @@ def run_gpu(args):
                         "api": "hmj_join_u64_host (pinned host buffers), %d joins in flight from %d host "
                                "threads with a context each; single_call = one join at a time" % (lanes, lanes)})
     elif world > 1 and not args.no_e2e:
-        # every rank: pinned host block of both relations -> H2D -> partition / all-to-all /
-        # sort / merge join -> D2H of this rank's pairs.  Wall clock between barriers, max over ranks.
+        # every rank: pinned host block of both relations -> H2D -> DistJoin.join_u64 -> D2H of this
+        # rank's pairs.  Wall clock between barriers, max over ranks.
         h_r = torch.empty(rows, dtype=torch.int64).pin_memory()
         h_s = torch.empty(rows, dtype=torch.int64).pin_memory()
         h_r.copy_(rkeys)
@@ -358,14 +358,18 @@ def run_gpu(args):
         cap = int(rows * 1.25) + 1024
         o_r = torch.empty(cap, dtype=torch.int32).pin_memory()
         o_s = torch.empty(cap, dtype=torch.int32).pin_memory()
+        import ctypes
+        o_ptr = [ctypes.c_void_p(o_r.data_ptr()), ctypes.c_void_p(o_s.data_ptr())]
 
         def e2e_step():
             rkeys.copy_(h_r, non_blocking=True)
             skeys.copy_(h_s, non_blocking=True)
-            m, (out_r, out_s, _, _) = joiner.join_u64(rkeys, skeys, want_pairs=True)
+            # the production path (level-1 scatter over NVLink, local bucket join); the rank's
+            # pairs (global row ids) leave from the context's result buffers
+            m = joiner.join_u64(rkeys, skeys)
             assert m <= cap
-            o_r[:m].copy_(out_r, non_blocking=True)
-            o_s[:m].copy_(out_s, non_blocking=True)
+            rc = ctx.lib.hmj_join_result_to_host(ctx.h, o_ptr[0], o_ptr[1], cap)
+            assert rc == 0, "hmj_join_result_to_host failed"
             torch.cuda.synchronize()
             return m
 
