@@ -4,6 +4,10 @@
 
 // Full-key verification of a candidate pair with string keys: the comparison the reference makes
 // after two hashes compare equal (/root/reference hashjoin.h:139-141, key == key).
+// Keys start at any byte of their chars column, so the two sides are seldom equally aligned:
+// each side is read as the aligned 8-byte words that hold its bytes and shifted into place
+// (little endian), 8 key bytes per step.  Only words holding at least one byte of the key are
+// touched (device allocations are whole multiples of 8 bytes, so such a word is always mapped).
 __device__ __forceinline__ bool keys_equal_str(const uint64_t* __restrict__ aoff,
                                                const uint8_t* __restrict__ achars, uint32_t arow,
                                                const uint64_t* __restrict__ boff,
@@ -12,21 +16,30 @@ __device__ __forceinline__ bool keys_equal_str(const uint64_t* __restrict__ aoff
   const uint64_t b0 = boff[brow], b1 = boff[brow + 1];
   const uint64_t len = a1 - a0;
   if (len != b1 - b0) return false;
-  const uint8_t* pa = achars + a0;
-  const uint8_t* pb = bchars + b0;
-  uint64_t i = 0;
-  // 8 bytes at a time when both sides are equally aligned, bytes otherwise
-  if (((reinterpret_cast<uintptr_t>(pa) ^ reinterpret_cast<uintptr_t>(pb)) & 7) == 0) {
-    while (i < len && (reinterpret_cast<uintptr_t>(pa + i) & 7)) {
-      if (pa[i] != pb[i]) return false;
-      ++i;
+  if (len == 0) return true;
+  const uintptr_t ua = reinterpret_cast<uintptr_t>(achars + a0);
+  const uintptr_t ub = reinterpret_cast<uintptr_t>(bchars + b0);
+  const uint64_t* wa = reinterpret_cast<const uint64_t*>(ua & ~uintptr_t(7));
+  const uint64_t* wb = reinterpret_cast<const uint64_t*>(ub & ~uintptr_t(7));
+  const uint32_t sa = (uint32_t)(ua & 7), sb = (uint32_t)(ub & 7);  // bytes to drop from the first word
+  uint64_t lo_a = wa[0], lo_b = wb[0];
+  for (uint64_t done = 0, k = 1;; done += 8, ++k) {
+    const uint64_t left = len - done;              // key bytes from this step on (>= 1)
+    const uint32_t take = left < 8 ? (uint32_t)left : 8u;
+    const bool more = left > 8;
+    // the step's bytes spill into the next aligned word when the key is not 8-aligned
+    const bool hi_a = sa + take > 8, hi_b = sb + take > 8;
+    const uint64_t na = (hi_a || more) ? wa[k] : 0, nb = (hi_b || more) ? wb[k] : 0;
+    uint64_t va = sa ? (lo_a >> (8 * sa)) | (na << (64 - 8 * sa)) : lo_a;
+    uint64_t vb = sb ? (lo_b >> (8 * sb)) | (nb << (64 - 8 * sb)) : lo_b;
+    if (take < 8) {
+      const uint64_t mask = (uint64_t(1) << (8 * take)) - 1;
+      va &= mask;
+      vb &= mask;
     }
-    for (; i + 8 <= len; i += 8)
-      if (*reinterpret_cast<const uint64_t*>(pa + i) != *reinterpret_cast<const uint64_t*>(pb + i))
-        return false;
+    if (va != vb) return false;
+    if (!more) return true;
+    lo_a = na;
+    lo_b = nb;
   }
-  for (; i < len; ++i)
-    if (pa[i] != pb[i]) return false;
-  return true;
 }
-
