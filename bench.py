@@ -349,6 +349,8 @@ def run_gpu(args):
                         "api": "hmj_join_u64_host (pinned host buffers), %d joins in flight from %d host "
                                "threads with a context each; single_call = one join at a time" % (lanes, lanes)})
     elif world > 1 and not args.no_e2e:
+        # the rank's pinned blocks should live on the NUMA node its GPU hangs off (first touch)
+        numa = bind_to_gpu_numa(local_rank)
         # every rank: pinned host block of both relations -> H2D -> DistJoin.join_u64 -> D2H of this
         # rank's pairs.  Wall clock between barriers, max over ranks.
         h_r = torch.empty(rows, dtype=torch.int64).pin_memory()
@@ -389,7 +391,8 @@ def run_gpu(args):
         assert int(t.item()) == rows_total
         e2e = {"value": 2 * rows_total / dt, "unit": UNIT, "h2d_bytes_per_step": 2 * rows_total * 8,
                "d2h_bytes_per_step": 2 * rows_total * 4, "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "api": "DistJoin.join_u64 (per-rank pinned host blocks; bytes are whole-job totals)"}
+               "api": "DistJoin.join_u64 (per-rank pinned host blocks; bytes are whole-job totals)",
+               "host_numa_cpus_rank0": numa}
 
     if rank == 0:
         cpu = None
@@ -428,6 +431,27 @@ def print_line(line):
     print(json.dumps(line), flush=True)
     if _REAL_STDOUT is not None:
         os.dup2(2, 1)
+
+
+def bind_to_gpu_numa(local_rank):
+    """Restrict this process to the CPUs local to its GPU (sysfs local_cpulist of the PCI device)
+    so that host buffers pinned afterwards are placed on that NUMA node.  Returns the CPU list, or
+    None when the topology is not exposed."""
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        txt = open("/sys/bus/pci/devices/%s/local_cpulist" % bdf).read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return txt
+    except Exception:
+        return None
 
 
 def main():

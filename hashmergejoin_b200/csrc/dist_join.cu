@@ -2,26 +2,30 @@
 //
 // every GPU splits its rows of R and S by hash range, one exchange moves range g
 // to GPU g, then every GPU joins its own range.  Here the split and the exchange are one kernel:
-// level 1 of the bucket scatter (bucket_scatter.cu) runs over the GPU's local rows with its
-// 2^b1 destination regions spread over the GPUs of the job -- region r belongs to GPU
-// r >> (b1 - log2 G) -- and writes every run straight into the owner's memory through NVLink peer
-// pointers.  Every source GPU owns a sub-region of every region (slot reservation = atomicAdd on
-// a cursor in the SOURCE's memory; the counts are handed to the owners after the kernel).  No
-// partition pass, no send buffers, no NCCL all-to-all; after a barrier every GPU continues locally with
-// level 2 and the bucket join on hash bits below the ones that chose the GPU.  It stands in for
-// partition_only's per-thread push_back into shared partitions (partitioned_hash.h:82-124) at
-// the scale of a node.
+// level 1 of the bucket scatter (bucket_scatter.cu) runs over the GPU's local rows, cuts them on
+// the top log2(G) hash bits -- exactly partition_only's h >> (64 - bits), partitioned_hash.h:59 --
+// and writes every run straight into the owner's memory through NVLink peer pointers (a 4096-pair
+// tile leaves as G runs of ~4096/G pairs: KBs per remote store).  Every source GPU owns a
+// sub-region of every destination (slot reservation = atomicAdd on a cursor in the SOURCE's
+// memory; the counts are handed to the owners after the kernel).  No partition pass, no send
+// buffers, no NCCL all-to-all; after a barrier every GPU cuts what it received on the bits below
+// in one or two local levels and runs the bucket join.  It stands in for partition_only's
+// per-thread push_back into shared partitions (partitioned_hash.h:82-124) at the scale of a node.
+// (First plan: level 1 cut on 9 bits, 512 regions spread over the GPUs -- runs of 16 pairs, 128-B
+// remote stores, ~300 GB/s of NVLink per GPU; C4 on 8 GPUs 13.4 ms.  GPU bits only: 10.0 ms.)
 //
 // One process per GPU: the regions are cudaMalloc'ed here and shared with CUDA IPC handles that
 // the caller exchanges over torch.distributed (hashmergejoin_b200/dist.py).
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
 struct hmj_dist_state {
   int world = 1, rank = 0;
-  int g_bits = 0, b1 = 0, b2 = 0, own_bits = 0;  // level-1 bits (job wide), level-2 bits, log2(own regions)
-  uint32_t cap1 = 0, cap_seg = 0, regions_own = 0;
+  // level-1 bits (job wide: the GPU bits + own_bits), local level bits (b3 = 0: one local level)
+  int g_bits = 0, b1 = 0, b2 = 0, b3 = 0, own_bits = 0;
+  uint32_t cap1 = 0, cap2 = 0, cap_seg = 0, regions_own = 0;
   // own level-1 regions per side (0 = R, 1 = S): regions_own x world sub-regions of cap1 slots
   // (keys, row ids) and their counts [regions_own * world], all shared with the peers;
   uint64_t* k1[2] = {nullptr, nullptr};
@@ -59,11 +63,32 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
     delete d;
     return hmj_fail(ctx, HMJ_EARG, "dist join: rows_total outside the supported range", __FILE__, __LINE__);
   }
-  d->b1 = (total_bits + 1) / 2;
-  if (d->b1 < d->g_bits + 1) d->b1 = d->g_bits + 1;
-  d->b2 = total_bits - d->b1;
+  // Level 1 splits on the GPU bits only: a tile then leaves as `world` runs of ~tile/world pairs
+  // (KBs per remote store instead of the 128 B of a 2^9-way split), and the bits below are cut
+  // locally in one or two more levels.  HMJ_DIST_L1_BITS widens level 1 (measurements).
+  d->b1 = d->g_bits;
+  if (const char* e = getenv("HMJ_DIST_L1_BITS")) {
+    const int v = atoi(e);
+    if (v > d->b1 && v <= 9 && v <= total_bits - 1) d->b1 = v;
+  }
+  const int rem = total_bits - d->b1;
+  if (rem <= 9) {
+    d->b2 = rem;
+    d->b3 = 0;
+  } else {
+    d->b2 = (rem + 1) / 2;
+    d->b3 = rem - d->b2;
+  }
   d->own_bits = d->b1 - d->g_bits;
   d->regions_own = 1u << d->own_bits;
+  if (d->b3 && ((size_t)d->regions_own << d->b2) > 512) {
+    delete d;
+    return hmj_fail(ctx, HMJ_EARG, "dist join: level-1 width leaves too many local regions", __FILE__, __LINE__);
+  }
+  if (d->b3) {
+    const double avg2 = (double)rows_total / (double)world / (double)((size_t)d->regions_own << d->b2);
+    d->cap2 = ((uint32_t)(avg2 + 8.0 * sqrt(avg2) + 64.0) + 255u) & ~255u;
+  }
   // a sub-region holds what ONE source sends to a region
   const double avg1 = (double)rows_total / (double)world / (double)(1u << d->b1);
   d->cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
@@ -156,22 +181,38 @@ extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
   cudaStream_t st = ctx->stream;
   *ok = 0;
   *h_num_pairs = 0;
-  const uint32_t buckets = d->regions_own << d->b2;
+  const uint32_t regions2 = d->regions_own << d->b2;        // after the first local level
+  const uint32_t buckets = regions2 << d->b3;               // final
   const size_t n_hint = d->rows_total / d->world;
   hmj_uniform_buckets B[2];
   for (int s = 0; s < 2; ++s) {
+    // scratch words: [8 spare][final cursors: buckets][middle cursors: regions2]
     uint32_t* words = nullptr;
-    HMJ_TRY(hmj_ws(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, (size_t)buckets + 8, &words));
-    HMJ_TRY(hmj_fill_async(ctx, words, 0, ((size_t)buckets + 8) * 4, st));
+    const size_t nwords = (size_t)8 + buckets + (d->b3 ? regions2 : 0);
+    HMJ_TRY(hmj_ws(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, nwords, &words));
+    HMJ_TRY(hmj_fill_async(ctx, words, 0, nwords * 4, st));
     uint64_t* k2 = nullptr;
     uint32_t* v2 = nullptr;
     const size_t slots2 = (size_t)buckets * d->cap_seg;
     HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, slots2, &k2));
     HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, slots2, &v2));
     uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);  // this rank's level-1 overflows land here too
-    HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1,
-                               d->regions_own * (uint32_t)d->world, n_hint, 64 - d->b1 - d->b2,
-                               d->b2, k2, v2, d->cap_seg, words + 8, flag, d->g_bits));
+    const uint32_t subs = d->regions_own * (uint32_t)d->world;
+    if (d->b3 == 0) {
+      HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
+                                 64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag, d->g_bits));
+    } else {
+      // sub-regions -> regions2 middle regions (one buffer, used by R then by S) -> final buckets
+      uint64_t* km = nullptr;
+      uint32_t* vm = nullptr;
+      uint32_t* cur_mid = words + 8 + buckets;
+      HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, (size_t)regions2 * d->cap2, &km));
+      HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, (size_t)regions2 * d->cap2, &vm));
+      HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
+                                 64 - d->b1 - d->b2, d->b2, km, vm, d->cap2, cur_mid, flag, d->g_bits));
+      HMJ_TRY(hmj_scatter_level2(ctx, km, vm, cur_mid, d->cap2, regions2, n_hint,
+                                 64 - d->b1 - d->b2 - d->b3, d->b3, k2, v2, d->cap_seg, words + 8, flag, 0));
+    }
     B[s].keys = k2;
     B[s].vals = v2;
     B[s].counts = words + 8;
@@ -179,7 +220,7 @@ extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
     B[s].flag = flag;
     B[s].buckets = buckets;
   }
-  return hmj_bucket_join_run(ctx, HMJ_KEY_U64, B[0], B[1], d->cap_seg, 64 - d->b1 - d->b2 - 12,
+  return hmj_bucket_join_run(ctx, HMJ_KEY_U64, B[0], B[1], d->cap_seg, 64 - d->b1 - d->b2 - d->b3 - 12,
                              n_hint, n_hint, nullptr, nullptr, nullptr, nullptr, h_num_pairs, ok);
 }
 
