@@ -21,10 +21,11 @@ def expected_pairs(rk, sk):
     order_s = np.argsort(sk, kind="stable")
     ss = sk[order_s]
     lo = np.searchsorted(ss, rk, side="left")
-    hi = np.searchsorted(ss, rk, side="right")
-    cnt = hi - lo
+    cnt = np.searchsorted(ss, rk, side="right") - lo
     r_idx = np.repeat(np.arange(rk.size), cnt)
-    offs = np.concatenate([np.arange(l, h) for l, h in zip(lo[cnt > 0], hi[cnt > 0])]) if cnt.sum() else np.empty(0, np.int64)
+    # position of every pair inside its run: running index minus the run's first index
+    first = np.repeat(np.cumsum(cnt) - cnt, cnt)
+    offs = np.repeat(lo, cnt) + (np.arange(r_idx.size) - first)
     return r_idx.astype(np.uint32), order_s[offs].astype(np.uint32)
 
 
