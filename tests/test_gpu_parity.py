@@ -540,6 +540,42 @@ def test_join_host_api(ctx, oracle):
     assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
 
 
+def test_host_joins_in_flight_from_two_threads(oracle):
+    # two host threads, a context (stream + workspace) each, host-buffer joins at the same time:
+    # the copy turns of host_api.cu must not mix up anyone's buffers
+    import threading
+    jobs = []
+    for seed in (3, 4):
+        keys = datagen.unique_u64(300000, seed=seed)
+        rk, sk = datagen.permuted(keys, 1).copy(), datagen.permuted(keys, 2)[:250000].copy()
+        rk[:100] = rk[100:200]
+        jobs.append((rk, sk, np.empty(300000, np.uint32), np.empty(300000, np.uint32)))
+    ctxs = [hmj.Context(0, use_torch_stream=False) for _ in jobs]
+    got = [[] for _ in jobs]
+    errors = []
+
+    def lane(i):
+        try:
+            rk, sk, out_r, out_s = jobs[i]
+            for _ in range(6):
+                got[i].append(ctxs[i].join_u64_host(rk, sk, out_r, out_s))
+        except Exception as e:  # surfaced below: an assert in a thread would go unseen
+            errors.append(e)
+
+    threads = [threading.Thread(target=lane, args=(i,)) for i in range(len(jobs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for i, (rk, sk, out_r, out_s) in enumerate(jobs):
+        t_r, t_s, _ = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+        assert got[i] == [t_r.size] * 6
+        c_r, c_s = oracle.sort_pairs(out_r[:t_r.size], out_s[:t_r.size])
+        assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+        ctxs[i].close()
+
+
 def test_sort_host_api(ctx, oracle):
     keys = np.random.default_rng(8).integers(0, 2 ** 64, size=77777, dtype=np.uint64)
     h, r = ctx.hash_sort_u64_host(keys)
