@@ -304,50 +304,62 @@ def run_gpu(args):
                "d2h_bytes_per_step": 2 * rows * 4, "ms_per_step": dt * 1e3, "steps": e2e_steps,
                "in_flight": 1, "api": "hmj_join_u64_host (pinned host buffers)"}
         if args.e2e_in_flight > 1:
-            # successive joins from `in_flight` host threads, one context (stream + workspace)
-            # each: a join's D2H of its pairs runs beside the next join's H2D of its keys (PCIe is
-            # full duplex); every join still copies its own inputs in and its own pairs out.
-            import threading
-            lanes = args.e2e_in_flight
-            # a stream of its own per lane (the default Context rides torch's current stream)
-            ctxs = [hmj.Context(local_rank, use_torch_stream=False) for _ in range(lanes)]
-            outs = [(a[2], a[3])]
-            for _ in range(lanes - 1):
-                p_r = torch.empty(rows, dtype=torch.int32).pin_memory()
-                p_s = torch.empty(rows, dtype=torch.int32).pin_memory()
-                outs.append((p_r.numpy().view(np.uint32), p_s.numpy().view(np.uint32)))
-            ctx.close()  # its workspace goes back before the lanes grow theirs
-            for c, (x, y) in zip(ctxs, outs):
-                c.join_u64_host(a[0], a[1], x, y)  # workspace growth
-            per_lane = max(4, e2e_steps)
-            got = [0] * lanes
+            try:
+                # successive joins from `in_flight` host threads, one context (stream + workspace)
+                # each: a join's D2H of its pairs runs beside the next join's H2D of its keys (PCIe is
+                # full duplex); every join still copies its own inputs in and its own pairs out.
+                import threading
+                lanes = args.e2e_in_flight
+                # a stream of its own per lane (the default Context rides torch's current stream)
+                ctxs = [hmj.Context(local_rank, use_torch_stream=False) for _ in range(lanes)]
+                outs = [(a[2], a[3])]
+                for _ in range(lanes - 1):
+                    p_r = torch.empty(rows, dtype=torch.int32).pin_memory()
+                    p_s = torch.empty(rows, dtype=torch.int32).pin_memory()
+                    outs.append((p_r.numpy().view(np.uint32), p_s.numpy().view(np.uint32)))
+                ctx.close()  # its workspace goes back before the lanes grow theirs
+                for c, (x, y) in zip(ctxs, outs):
+                    c.join_u64_host(a[0], a[1], x, y)  # workspace growth
+                per_lane = max(4, e2e_steps)
+                got = [0] * lanes
 
-            def lane(i):
-                # staggered start: joins entering together would queue on the same copy engine
-                # at the same time and leave it together
-                time.sleep(i * dt / lanes)
-                for _ in range(per_lane):
-                    got[i] = ctxs[i].join_u64_host(a[0], a[1], *outs[i])
+                lane_errors = []
 
-            th = [threading.Thread(target=lane, args=(i,)) for i in range(lanes)]
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for t in th:
-                t.start()
-            for t in th:
-                t.join()
-            torch.cuda.synchronize()
-            dtp = (time.perf_counter() - t0) / (per_lane * lanes)
-            assert all(g == rows for g in got)
-            for x, y in outs:
-                assert (a[0][x[:1000]] == a[1][y[:1000]]).all(), "pipelined e2e result pairs do not join equal keys"
-            for c in ctxs:
-                c.close()
-            e2e.update({"single_call": {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"]},
-                        "value": 2 * rows / dtp, "ms_per_step": dtp * 1e3, "steps": per_lane * lanes,
-                        "in_flight": lanes,
-                        "api": "hmj_join_u64_host (pinned host buffers), %d joins in flight from %d host "
-                               "threads with a context each; single_call = one join at a time" % (lanes, lanes)})
+                def lane(i):
+                    # staggered start: joins entering together would queue on the same copy engine
+                    # at the same time and leave it together
+                    try:
+                        time.sleep(i * dt / lanes)
+                        for _ in range(per_lane):
+                            got[i] = ctxs[i].join_u64_host(a[0], a[1], *outs[i])
+                    except Exception as e:  # re-raised on the main thread below
+                        lane_errors.append(e)
+
+                th = [threading.Thread(target=lane, args=(i,)) for i in range(lanes)]
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for t in th:
+                    t.start()
+                for t in th:
+                    t.join()
+                torch.cuda.synchronize()
+                dtp = (time.perf_counter() - t0) / (per_lane * lanes)
+                if lane_errors:
+                    raise lane_errors[0]
+                assert all(g == rows for g in got)
+                for x, y in outs:
+                    assert (a[0][x[:1000]] == a[1][y[:1000]]).all(), "pipelined e2e result pairs do not join equal keys"
+                for c in ctxs:
+                    c.close()
+                e2e.update({"single_call": {"value": e2e["value"], "ms_per_step": e2e["ms_per_step"]},
+                            "value": 2 * rows / dtp, "ms_per_step": dtp * 1e3, "steps": per_lane * lanes,
+                            "in_flight": lanes,
+                            "api": "hmj_join_u64_host (pinned host buffers), %d joins in flight from %d host "
+                                   "threads with a context each; single_call = one join at a time" % (lanes, lanes)})
+            except (RuntimeError, MemoryError, hmj.HmjError) as e:
+                # no room for a second lane (device workspace or pinned host memory): the
+                # one-at-a-time figure stands; wrong results are assertion errors and not caught
+                e2e["in_flight_error"] = str(e)[:200]
     elif world > 1 and not args.no_e2e:
         # the rank's pinned blocks should live on the NUMA node its GPU hangs off (first touch)
         numa = bind_to_gpu_numa(local_rank)
