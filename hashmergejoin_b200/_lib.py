@@ -45,6 +45,7 @@ class Timings(C.Structure):
         ("sort_finishes", C.c_uint32), ("sort_fallbacks", C.c_uint32),
         ("sort_uniform", C.c_uint32), ("kernel_launches", C.c_uint32 * 8),
         ("kernel_ms", C.c_float * 8), ("kernel_bytes", C.c_double * 8),
+        ("bucket_join", C.c_uint32), ("scatter_levels", C.c_uint32),
     ]
 
 
@@ -94,10 +95,14 @@ SIGNATURES = {
     "hmj_get_timings": (_I, [_P, C.POINTER(Timings)]),
     "hmj_dist_setup": (_I, [_P, _I, _I, _SZ, _P]),
     "hmj_dist_connect": (_I, [_P, _P]),
-    "hmj_dist_begin": (_I, [_P]),
-    "hmj_dist_scatter": (_I, [_P, _I, _P, _SZ, C.c_uint32]),
-    "hmj_dist_join": (_I, [_P, _U64P, C.POINTER(C.c_int)]),
+    "hmj_dist_handle_bytes": (_I, []),
+    "hmj_dist_join_u64": (_I, [_P, _P, _SZ, C.c_uint32, _P, _SZ, C.c_uint32, _U64P, C.POINTER(C.c_int)]),
+    "hmj_dist_last_exchange": (_I, [_P, _U64P, _U64P, _U64P]),
     "hmj_dist_teardown": (_I, [_P]),
+    "hmj_gen_permute": (_I, [_P, _P, C.c_uint32, _SZ, C.c_uint32, C.c_uint32, _P]),
+    "hmj_gen_zipf": (_I, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _SZ, _P]),
+    "hmj_gen_strgen_lengths": (_I, [_P, _P, C.c_uint32, _P, _SZ, _P]),
+    "hmj_gen_strgen_write": (_I, [_P, _P, _P, C.c_uint32, _P, _SZ, _P, _P]),
 }
 
 _lib = None

@@ -186,7 +186,7 @@ class Context:
 
     # ---- multi-GPU join, exchange fused into the first scatter level (dist_join.cu)
     def dist_setup(self, rank, world, rows_total):
-        handles = np.zeros(6 * 64, np.uint8)
+        handles = np.zeros(self.lib.hmj_dist_handle_bytes(), np.uint8)
         self._ck(self.lib.hmj_dist_setup(self.h, rank, world, rows_total, _hptr(handles)))
         return handles
 
@@ -194,17 +194,24 @@ class Context:
         all_handles = np.ascontiguousarray(all_handles, np.uint8)
         self._ck(self.lib.hmj_dist_connect(self.h, _hptr(all_handles)))
 
-    def dist_begin(self):
-        self._ck(self.lib.hmj_dist_begin(self.h))
-
-    def dist_scatter(self, side, keys, rowid_base):
-        _check_dev(keys, 8)
-        self._ck(self.lib.hmj_dist_scatter(self.h, side, _dptr(keys), keys.numel(), rowid_base))
-
-    def dist_join(self):
+    def dist_join_u64(self, rkeys, r_rowid_base, skeys, s_rowid_base):
+        """hmj_dist_join_u64 -> (pairs of this rank's hash range, ok)"""
+        _check_dev(rkeys, 8)
+        _check_dev(skeys, 8)
         m, ok = C.c_uint64(), C.c_int()
-        self._ck(self.lib.hmj_dist_join(self.h, C.byref(m), C.byref(ok)))
+        self._ck(self.lib.hmj_dist_join_u64(self.h, _dptr(rkeys), rkeys.numel(), r_rowid_base,
+                                            _dptr(skeys), skeys.numel(), s_rowid_base,
+                                            C.byref(m), C.byref(ok)))
         return m.value, ok.value
+
+    def dist_last_exchange(self):
+        """(pairs written into other ranks' memory, R pairs received, S pairs received)"""
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.hmj_dist_last_exchange(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def dist_teardown(self):
+        self._ck(self.lib.hmj_dist_teardown(self.h))
 
     def join_strings(self, roff, rchars, soff, schars, prefix_bits=0):
         """hmj_join_strings[_range]: prefix_bits > 0 when every key hashes into one hash range
@@ -294,6 +301,36 @@ class Context:
         self._ck(self.lib.hmj_hashjoin_build_probe(self.h, C.byref(r), C.byref(s), _dptr(rvals),
                                                    _dptr(svals), C.byref(hits), C.byref(sm)))
         return hits.value, sm.value
+
+    # ---- device generators of the benchmark relations (datagen.cu)
+    def gen_permute(self, n, domain, seed, src=None, base=0):
+        """int32 tensor: P(src[i]) or P(base + i), P a seeded bijection of [0, domain)"""
+        out = self._empty(n, self._torch.int32)
+        self._ck(self.lib.hmj_gen_permute(self.h, _dptr(src), base, n, domain, seed & 0xFFFFFFFF, _dptr(out)))
+        return out
+
+    def gen_zipf(self, cdf, n, seed, row_base=0):
+        """int32 tensor of n ranks drawn from the float64 device prefix table `cdf`"""
+        assert cdf.is_cuda and cdf.dtype == self._torch.float64 and cdf.is_contiguous()
+        out = self._empty(n, self._torch.int32)
+        self._ck(self.lib.hmj_gen_zipf(self.h, _dptr(cdf), cdf.numel(), seed, row_base, n, _dptr(out)))
+        return out
+
+    def gen_strgen(self, word_offsets, word_chars, key_ids):
+        """(offsets int64[n+1], chars uint8[]) of the strgen keys `key_ids` (int32 tensor)"""
+        t = self._torch
+        n, q = key_ids.numel(), word_offsets.numel() - 1
+        lens = self._empty(n, t.int64)
+        self._ck(self.lib.hmj_gen_strgen_lengths(self.h, _dptr(word_offsets), q, _dptr(key_ids), n, _dptr(lens)))
+        off = t.zeros(n + 1, dtype=t.int64, device=self.device)
+        if n:
+            t.cumsum(lens, 0, out=off[1:])
+        del lens
+        total = int(off[-1].item()) if n else 0
+        chars = self._empty(total + 16, t.uint8)[:total]   # padded: readers may look one word ahead
+        self._ck(self.lib.hmj_gen_strgen_write(self.h, _dptr(word_offsets), _dptr(word_chars), q,
+                                               _dptr(key_ids), n, _dptr(off), _dptr(chars)))
+        return off, chars
 
     # ---- misc
     def synchronize(self):

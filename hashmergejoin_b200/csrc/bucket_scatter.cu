@@ -18,6 +18,10 @@
 // caller then runs the histogram-planned stable sort on the untouched input.
 // Algorithmic bytes per pair: level 1 reads 8 (+4 with row ids) and writes 12; level 2 reads 12
 // and writes 12; finish reads 12 and writes 12.
+#include <math.h>
+
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -145,11 +149,25 @@ bucket_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
 // load latency: profiles/r1d, 54 % of its stall samples).  The tile is permuted in place in its
 // buffer and leaves with coalesced stores.
 constexpr int UT_ITEMS = 8;
-template <int THREADS>
+// RANK: how an item gets its slot inside its digit's run of the tile.
+//   0  one shared-memory atomicAdd per item on the tile's digit counters.  ATOMS on spread
+//      addresses is served lane by lane (~0.6 cycles per lane measured here; the LSU pipe was the
+//      kernel's limiter at 70 % wavefront utilisation, about half of it these atomics).
+//   1  warp-private digit counters (u16, [warps][256]) and a warp-level multisplit: lanes with
+//      the same digit find each other with match.any, take their rank from the lane mask, the
+//      group's first lane bumps the warp's counter with a plain load + store; a column scan over
+//      the warps then gives every warp its base inside the digit's run.  No shared-memory atomics.
+//   2  as 1 with the peer mask built from one ballot per digit bit instead of match.any.
+// 1 and 2 need bins <= 256 (the 512-thread configurations); the 9-bit levels keep 0.
+template <int THREADS, int RANK>
 struct UtCfg {
   static constexpr int TILE = THREADS * UT_ITEMS;
+  static constexpr int WARPS = THREADS / 32;
+  static constexpr int BINS = THREADS > 512 ? 512 : 256;   // most bins a level of this shape cuts
   static constexpr size_t BUF_BYTES = (size_t)TILE * 12;
-  static constexpr size_t SMEM = 2 * BUF_BYTES + 4 * US_MAX_BINS * 4 + 32 * 4 + 64 + 16 * 8;
+  static constexpr size_t WCNT_BYTES = RANK ? (size_t)WARPS * 256 * 2 : 0;
+  // buffers, [cnt][off][gbase] per bin, region counts (<= 512), warp counters, scan, bars, peers
+  static constexpr size_t SMEM = 2 * BUF_BYTES + 3 * BINS * 4 + 512 * 4 + WCNT_BYTES + 32 * 4 + 64 + 16 * 8;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -194,7 +212,7 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
 // region_shift (level 2 of such a job): input region t / tiles_per_region is a sub-region; the
 // bucket prefix is the region it belongs to, (t / tiles_per_region) >> region_shift.
 
-template <int UT_THREADS, int MIN_BLOCKS, bool DIST>
+template <int UT_THREADS, int MIN_BLOCKS, bool DIST, int RANK>
 __global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
 bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           const uint32_t* __restrict__ in_counts, uint32_t in_stride,
@@ -202,20 +220,33 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
                           uint32_t iota_base, uint64_t* __restrict__ keys_out,
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
                           uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag,
-                          const hmj_peer_regions peers, int region_shift) {
-  constexpr int UT_TILE = UtCfg<UT_THREADS>::TILE;
-  constexpr size_t UT_BUF_BYTES = UtCfg<UT_THREADS>::BUF_BYTES;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_raw + 2 * UT_BUF_BYTES);
-  uint32_t* s_off = s_cnt + US_MAX_BINS;
-  uint32_t* s_gbase = s_off + US_MAX_BINS;
-  uint32_t* s_rcount = s_gbase + US_MAX_BINS;  // [regions <= 256] pairs per input region
-  uint32_t* s_scan = s_rcount + US_MAX_BINS;   // [32]
+                          uint32_t* __restrict__ tile_counter, const hmj_peer_regions peers,
+                          int region_shift) {
+  using Cfg = UtCfg<UT_THREADS, RANK>;
+  constexpr int UT_TILE = Cfg::TILE;
+  constexpr size_t UT_BUF_BYTES = Cfg::BUF_BYTES;
+  extern __shared__ __align__(128) unsigned char smem_tma[];
+  uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_tma + 2 * UT_BUF_BYTES);
+  uint32_t* s_off = s_cnt + Cfg::BINS;
+  uint32_t* s_gbase = s_off + Cfg::BINS;
+  uint32_t* s_rcount = s_gbase + Cfg::BINS;    // [regions <= 512] pairs per input region
+  uint16_t* s_wcnt = reinterpret_cast<uint16_t*>(s_rcount + 512);  // [warps][256] (RANK != 0)
+  uint32_t* s_scan = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(s_wcnt) + Cfg::WCNT_BYTES);  // [32]
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_scan + 32);  // [2]
   uint64_t** s_pk = reinterpret_cast<uint64_t**>(s_bar + 2);   // [8] peer key columns (DIST)
   uint32_t** s_pv = reinterpret_cast<uint32_t**>(s_pk + 8);    // [8] peer row-id columns
+  uint32_t* s_next = reinterpret_cast<uint32_t*>(s_pv + 8);    // [2] tile ids handed to the CTA
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // Tiles are handed out by a global counter, not by block index: a CTA that starts late (the
+  // kernel shares the SMs with another stream's kernel in the multi-GPU join) simply takes fewer
+  // tiles.  The id of the tile after next is fetched one iteration ahead, so the atomic's round
+  // trip never shows.
+  if (tid == 0) {
+    const uint32_t v = atomicAdd(tile_counter, 2u);
+    s_next[0] = v;
+    s_next[1] = v + 1;
+  }
   if (DIST && tid < 8) {
     s_pk[tid] = peers.keys[tid];
     s_pv[tid] = peers.vals[tid];
@@ -251,7 +282,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     const uint32_t valid = t < total_tiles ? tile_of(t, &in_base) : 0;
     if (valid != (uint32_t)UT_TILE) return false;
     if (tid == 0) {
-      unsigned char* buf = smem_raw + (size_t)b * UT_BUF_BYTES;
+      unsigned char* buf = smem_tma + (size_t)b * UT_BUF_BYTES;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       const uint32_t bytes = UT_TILE * 8 + (vals_in ? UT_TILE * 4 : 0);
       mbar_expect_tx(&s_bar[b], bytes);
@@ -262,24 +293,38 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
   };
 
   uint32_t phase[2] = {0, 0};
-  bool pending_next = issue(blockIdx.x, 0);
-  int it = 0;
-  for (uint32_t t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+  uint32_t t = s_next[0], t_next = s_next[1];
+  __syncthreads();  // s_next is rewritten from the first iteration on
+  bool pending_next = issue(t, 0);
+  for (int it = 0; t < total_tiles; ++it) {
     const int b = it & 1;
     const bool pending_cur = pending_next;
-    pending_next = issue(t + gridDim.x, b ^ 1);
+    pending_next = issue(t_next, b ^ 1);
+    uint32_t fetched = 0;
+    if (tid == 0) fetched = atomicAdd(tile_counter, 1u);
     uint32_t in_base = 0;
     const uint32_t valid = tile_of(t, &in_base);
-    if (valid == 0) continue;
+    if (valid == 0) {
+      if (tid == 0) s_next[b] = fetched;
+      __syncthreads();
+      t = t_next;
+      t_next = s_next[b];
+      continue;
+    }
     if (__syncthreads_or(tid == 0 && *reinterpret_cast<volatile uint32_t*>(flag) != 0)) {
       // never leave with a bulk copy still writing into this CTA's shared memory
       if (pending_cur) mbar_wait(&s_bar[b], phase[b]);
       if (pending_next) mbar_wait(&s_bar[b ^ 1], phase[b ^ 1]);
       return;
     }
-    uint64_t* b_keys = reinterpret_cast<uint64_t*>(smem_raw + (size_t)b * UT_BUF_BYTES);
+    uint64_t* b_keys = reinterpret_cast<uint64_t*>(smem_tma + (size_t)b * UT_BUF_BYTES);
     uint32_t* b_vals = reinterpret_cast<uint32_t*>(b_keys + UT_TILE);
-    if (tid < bins) s_cnt[tid] = 0;
+    if (RANK == 0) {
+      if (tid < bins) s_cnt[tid] = 0;
+    } else {
+      // the warp's own counters (256 x u16 = 512 bytes: one 16-byte store per lane)
+      reinterpret_cast<uint4*>(s_wcnt + warp * 256)[lane] = make_uint4(0, 0, 0, 0);
+    }
     if (pending_cur) {
       mbar_wait(&s_bar[b], phase[b]);
       phase[b] ^= 1;
@@ -293,17 +338,60 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 
     uint64_t key[UT_ITEMS];
     uint16_t slot[UT_ITEMS];
+    if (RANK == 0) {
 #pragma unroll
-    for (int k = 0; k < UT_ITEMS; ++k) {
-      const uint32_t i = tid + k * UT_THREADS;
-      if (i < valid) {
-        key[k] = b_keys[i];
-        slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+      for (int k = 0; k < UT_ITEMS; ++k) {
+        const uint32_t i = tid + k * UT_THREADS;
+        if (i < valid) {
+          key[k] = b_keys[i];
+          slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+        }
+      }
+    } else {
+      uint16_t* wc = s_wcnt + warp * 256;
+      const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+      for (int k = 0; k < UT_ITEMS; ++k) {
+        const uint32_t i = tid + k * UT_THREADS;
+        const bool live = i < valid;
+        key[k] = live ? b_keys[i] : 0;
+        // rows past the end of a partial tile share the digit 256, which no counter holds
+        const uint32_t dig = live ? (uint32_t)(key[k] >> shift) & mask : 256u;
+        uint32_t peers_of;
+        if (RANK == 1) {
+          peers_of = __match_any_sync(0xffffffffu, dig);
+        } else {
+          peers_of = 0xffffffffu;
+#pragma unroll
+          for (int bit = 0; bit < 9; ++bit) {
+            const bool one = (dig >> bit) & 1u;
+            const uint32_t bl = __ballot_sync(0xffffffffu, one);
+            peers_of &= one ? bl : ~bl;
+          }
+        }
+        const uint32_t rank = __popc(peers_of & lt);
+        uint32_t base = 0;
+        if (live) base = wc[dig];
+        __syncwarp();
+        if (live && rank == 0) wc[dig] = (uint16_t)(base + __popc(peers_of));
+        __syncwarp();
+        slot[k] = (uint16_t)(base + rank);
       }
     }
     __syncthreads();
 
     uint32_t c = 0, old = 0, bucket = 0;
+    if (RANK != 0 && tid < bins) {
+      // column scan: warp w's base inside the digit's run = pairs of the warps before it
+      uint32_t run = 0;
+#pragma unroll
+      for (int w = 0; w < Cfg::WARPS; ++w) {
+        const uint32_t x = s_wcnt[w * 256 + tid];
+        s_wcnt[w * 256 + tid] = (uint16_t)run;
+        run += x;
+      }
+      s_cnt[tid] = run;
+    }
     if (tid < bins) {
       c = s_cnt[tid];
       bucket = (((t / tiles_per_region) >> region_shift) << bits) | (uint32_t)tid;
@@ -329,7 +417,15 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       uint32_t wt = lane < warp ? s_scan[lane] : 0;  // 16 warps
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
-      if (tid < bins) s_off[tid] = wt + x - c;
+      if (tid < bins) {
+        const uint32_t off = wt + x - c;
+        s_off[tid] = off;
+        if (RANK != 0) {
+          // fold the digit's start into the warps' bases: one lookup per item below
+#pragma unroll
+          for (int w = 0; w < Cfg::WARPS; ++w) s_wcnt[w * 256 + tid] += (uint16_t)off;
+        }
+      }
     }
     __syncthreads();  // s_off ready; every thread holds its keys and row ids in registers
 
@@ -337,7 +433,8 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
       if (i < valid) {
-        const uint32_t p = s_off[(uint32_t)(key[k] >> shift) & mask] + slot[k];
+        const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
+        const uint32_t p = (RANK == 0 ? s_off[d] : (uint32_t)s_wcnt[warp * 256 + d]) + slot[k];
         b_keys[p] = key[k];
         b_vals[p] = val[k];
       }
@@ -366,7 +463,10 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
         vals_out[dst] = b_vals[i];
       }
     }
+    if (tid == 0) s_next[b] = fetched;
     __syncthreads();  // the buffer may be refilled from here on
+    t = t_next;
+    t_next = s_next[b];
   }
 }
 
@@ -420,6 +520,69 @@ int uniform_from_env() {
   return e ? atoi(e) : 1;
 }
 
+// HMJ_SCATTER_RANK: 0 = shared-memory atomics, 1 = match.any multisplit (default), 2 = ballot
+// multisplit (see UtCfg)
+int rank_from_env() {
+  static const int v = [] {
+    const char* e = getenv("HMJ_SCATTER_RANK");
+    const int r = e ? atoi(e) : 1;
+    return r < 0 || r > 2 ? 1 : r;
+  }();
+  return v;
+}
+
+struct ScatterLaunch {
+  const uint64_t* keys_in; const uint32_t* vals_in; const uint32_t* in_counts;
+  uint32_t in_stride, n_single, tiles_per_region, total_tiles, iota_base;
+  uint64_t* keys_out; uint32_t* vals_out;
+  int shift, bits;
+  uint32_t out_cap;
+  uint32_t *cursors, *flag, *tile_counter;  // tile_counter: zeroed by the caller
+  const hmj_peer_regions* peers;            // != nullptr: regions on the GPUs of the job (level 1)
+  int region_shift;
+};
+
+template <int T, int B, bool DIST, int RANK>
+int launch_tma(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
+  using Cfg = UtCfg<T, RANK>;
+  static_assert(Cfg::SMEM * B + 1024 * B <= 233472, "scatter configuration does not fit an SM");
+  auto* kern = bucket_scatter_tma_kernel<T, B, DIST, RANK>;
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+  const uint32_t per_sm = ctas_per_sm == 0 || ctas_per_sm > (uint32_t)B ? (uint32_t)B : ctas_per_sm;
+  const uint32_t grid = std::min(a.total_tiles, (uint32_t)ctx->num_sms * per_sm);
+  kern<<<grid, T, Cfg::SMEM, st>>>(a.keys_in, a.vals_in, a.in_counts, a.in_stride, a.n_single,
+                                   a.tiles_per_region, a.total_tiles, a.iota_base, a.keys_out,
+                                   a.vals_out, a.shift, a.bits, a.out_cap, a.cursors, a.flag,
+                                   a.tile_counter, a.peers ? *a.peers : hmj_peer_regions(),
+                                   a.region_shift);
+  HMJ_LAUNCHED(ctx);
+  ctx->tm.scatter_levels++;
+  return HMJ_OK;
+}
+
+// pairs per tile of the configuration a level of `bits` bits runs with
+uint32_t tile_items_for(int bits) { return bits > 8 ? 8192u : 4096u; }
+
+// One bucket-scatter launch (TMA-pipelined kernel).  ctas_per_sm = 0: as many as fit.
+int launch_scatter(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
+  if (a.total_tiles == 0) return HMJ_OK;
+  const bool dist = a.peers != nullptr;
+  if (a.bits > 8)  // 512 bins: 1024-thread tiles of 8192 pairs, shared-memory atomics
+    return dist ? launch_tma<1024, 1, true, 0>(ctx, a, ctas_per_sm, st)
+                : launch_tma<1024, 1, false, 0>(ctx, a, ctas_per_sm, st);
+  switch (rank_from_env()) {
+    case 0:
+      return dist ? launch_tma<512, 2, true, 0>(ctx, a, ctas_per_sm, st)
+                  : launch_tma<512, 2, false, 0>(ctx, a, ctas_per_sm, st);
+    case 2:
+      return dist ? launch_tma<512, 2, true, 2>(ctx, a, ctas_per_sm, st)
+                  : launch_tma<512, 2, false, 2>(ctx, a, ctas_per_sm, st);
+    default:
+      return dist ? launch_tma<512, 2, true, 1>(ctx, a, ctas_per_sm, st)
+                  : launch_tma<512, 2, false, 1>(ctx, a, ctas_per_sm, st);
+  }
+}
+
 }  // namespace
 
 // Final buckets of at most 4096 pairs on average for `n_plan` rows (the larger relation of a
@@ -461,7 +624,7 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
     const double avg1 = (double)n / (double)regions1;
     cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
   }
-  // scratch words: [flag][level-1 cursors][final cursors][final offsets + 1]
+  // scratch words: [flag, tile counters: 8 words][level-1 cursors][final cursors][final offsets + 1]
   uint32_t* d_words = nullptr;
   const size_t words = 8 + (size_t)regions1 + buckets + buckets + 1;
   HMJ_TRY(hmj_ws(ctx, set ? WS_US_CURSORS_1 : WS_US_CURSORS, words, &d_words));
@@ -480,60 +643,58 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
     HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, slots1, &d_k1));
     HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, slots1, &d_v1));
   }
-  HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
   // bulk copies need 16-byte aligned sources (tile starts are multiples of 4096 pairs)
   const bool tma = uniform_from_env() != 2 && (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 &&
                    (reinterpret_cast<uintptr_t>(vals_in) & 15) == 0;
   const bool wide = p.bits[0] > 8 || p.bits[1] > 8;  // 512 bins: 1024-thread tiles of 8192 pairs
   HMJ_ARG(ctx, tma || !wide);
-  const char* ecfg = getenv("HMJ_SCATTER_CFG");
-  const int scfg = wide ? 3 : ecfg ? atoi(ecfg) : 0;
   cudaEvent_t ev;
   // level 1: the raw key column -> 2^bits[0] regions
-  const uint32_t tile_items = !tma ? US_TILE : scfg == 1 ? 2048 : scfg == 2 ? 3072 : scfg == 3 ? 8192 : 4096;
-  const uint32_t tiles = (uint32_t)hmj_div_up(n, tile_items);
-#define HMJ_TMA_LAUNCH(T, B, NT, ...)                                                              \
-  do {                                                                                            \
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<T, B, false>,                    \
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,               \
-                                       (int)UtCfg<T>::SMEM));                                     \
-    bucket_scatter_tma_kernel<T, B, false><<<min((uint32_t)(NT), (uint32_t)ctx->num_sms * B), T,  \
-                                             UtCfg<T>::SMEM, st>>>(__VA_ARGS__, hmj_peer_regions(), 0); \
-  } while (0)
-#define HMJ_TMA_DISPATCH(NT, ...)                                     \
-  do {                                                               \
-    if (scfg == 1) HMJ_TMA_LAUNCH(256, 4, NT, __VA_ARGS__);           \
-    else if (scfg == 2) HMJ_TMA_LAUNCH(384, 3, NT, __VA_ARGS__);      \
-    else if (scfg == 3) HMJ_TMA_LAUNCH(1024, 1, NT, __VA_ARGS__);     \
-    else HMJ_TMA_LAUNCH(512, 2, NT, __VA_ARGS__);                     \
-  } while (0)
   uint64_t* k_out1 = p.levels == 2 ? d_k1 : d_k2;
   uint32_t* v_out1 = p.levels == 2 ? d_v1 : d_v2;
   const uint32_t cap_out1 = p.levels == 2 ? cap1 : p.cap_seg;
-  if (tiles) {
+  if (n) {
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * (vals_in ? 24.0 : 20.0), &ev));
-    if (tma)
-      HMJ_TMA_DISPATCH(tiles, keys_in, vals_in, nullptr, 0, n32, tiles, tiles, iota_base, k_out1, v_out1,
-                       64 - p.skip - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
-    else
+    if (tma) {
+      ScatterLaunch a = {};
+      a.keys_in = keys_in; a.vals_in = vals_in; a.n_single = n32; a.iota_base = iota_base;
+      a.total_tiles = (uint32_t)hmj_div_up(n, tile_items_for(p.bits[0]));
+      a.tiles_per_region = a.total_tiles;
+      a.keys_out = k_out1; a.vals_out = v_out1;
+      a.shift = 64 - p.skip - p.bits[0]; a.bits = p.bits[0]; a.out_cap = cap_out1;
+      a.cursors = d_cur1; a.flag = d_flag; a.tile_counter = d_words + 1;
+      HMJ_TRY(launch_scatter(ctx, a, 0, st));
+    } else {
+      HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
+      const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);
       bucket_scatter_kernel<<<tiles, US_THREADS, US_SMEM, st>>>(
           keys_in, vals_in, nullptr, 0, n32, tiles, iota_base, k_out1, v_out1,
           64 - p.skip - p.bits[0], p.bits[0], cap_out1, d_cur1, d_flag);
-    HMJ_LAUNCHED(ctx);
+      HMJ_LAUNCHED(ctx);
+      ctx->tm.scatter_levels++;
+    }
     hmj_prof_end(ctx, ev);
   }
-  if (p.levels == 2 && tiles) {
-    const uint32_t tpr = (uint32_t)hmj_div_up(cap1, tile_items);
+  if (p.levels == 2 && n) {
     HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 24.0, &ev));
-    if (tma)
-      HMJ_TMA_DISPATCH(regions1 * tpr, d_k1, d_v1, d_cur1, cap1, 0, tpr, regions1 * tpr, 0, d_k2, d_v2,
-                       64 - p.skip - p.qb, p.bits[1], p.cap_seg, d_cur2, d_flag);
-    else
+    if (tma) {
+      ScatterLaunch a = {};
+      a.keys_in = d_k1; a.vals_in = d_v1; a.in_counts = d_cur1; a.in_stride = cap1;
+      a.tiles_per_region = (uint32_t)hmj_div_up(cap1, tile_items_for(p.bits[1]));
+      a.total_tiles = regions1 * a.tiles_per_region;
+      a.keys_out = d_k2; a.vals_out = d_v2;
+      a.shift = 64 - p.skip - p.qb; a.bits = p.bits[1]; a.out_cap = p.cap_seg;
+      a.cursors = d_cur2; a.flag = d_flag; a.tile_counter = d_words + 2;
+      HMJ_TRY(launch_scatter(ctx, a, 0, st));
+    } else {
+      const uint32_t tpr = (uint32_t)hmj_div_up(cap1, US_TILE);
       bucket_scatter_kernel<<<regions1 * tpr, US_THREADS, US_SMEM, st>>>(
           d_k1, d_v1, d_cur1, cap1, 0, tpr, 0, d_k2, d_v2, 64 - p.skip - p.qb, p.bits[1],
           p.cap_seg, d_cur2, d_flag);
-    HMJ_LAUNCHED(ctx);
+      HMJ_LAUNCHED(ctx);
+      ctx->tm.scatter_levels++;
+    }
     hmj_prof_end(ctx, ev);
   }
   out->keys = d_k2;
@@ -574,70 +735,48 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
 
 // ---- launch helpers of the multi-GPU join (dist_join.cu) --------------------------------
 // Level 1 of the job on this rank's rows: regions are spread over the GPUs (peer pointers).
-int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
-                            int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
-                            uint32_t* d_cursors, uint32_t* d_flag) {
-  if (n == 0) return HMJ_OK;
+// d_cursors: [2^bits cursors][flag][tile counter], zeroed by the caller.  The rank's counts are
+// handed to the owners of the regions even when it has no rows (they must not see old ones).
+int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_in, size_t n,
+                            uint32_t iota_base, int shift, int bits, uint32_t out_cap,
+                            const hmj_peer_regions& peers, uint32_t* d_cursors, uint32_t* d_flag,
+                            uint32_t ctas_per_sm) {
   HMJ_ARG(ctx, (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 && bits <= 9);
-  cudaStream_t st = ctx->stream;
-  cudaEvent_t ev;
-  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n * 20.0, &ev));
-  if (bits > 8) {
-    const uint32_t tiles = (uint32_t)hmj_div_up(n, UtCfg<1024>::TILE);
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<1024, 1, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)UtCfg<1024>::SMEM));
-    bucket_scatter_tma_kernel<1024, 1, true><<<min(tiles, (uint32_t)ctx->num_sms), 1024,
-                                               UtCfg<1024>::SMEM, st>>>(
-        keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
-        bits, out_cap, d_cursors, d_flag, peers, 0);
-  } else {
-    const uint32_t tiles = (uint32_t)hmj_div_up(n, UtCfg<512>::TILE);
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<512, 2, true>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)UtCfg<512>::SMEM));
-    bucket_scatter_tma_kernel<512, 2, true><<<min(tiles, (uint32_t)ctx->num_sms * 2), 512,
-                                              UtCfg<512>::SMEM, st>>>(
-        keys_in, nullptr, nullptr, 0, (uint32_t)n, tiles, tiles, iota_base, nullptr, nullptr, shift,
-        bits, out_cap, d_cursors, d_flag, peers, 0);
+  if (n) {
+    cudaEvent_t ev;
+    HMJ_TRY(hmj_prof_begin_on(ctx, HMJ_K_XSCATTER, (double)n * 20.0, &ev, st));
+    ScatterLaunch a = {};
+    a.keys_in = keys_in; a.n_single = (uint32_t)n; a.iota_base = iota_base;
+    a.total_tiles = (uint32_t)hmj_div_up(n, tile_items_for(bits));
+    a.tiles_per_region = a.total_tiles;
+    a.shift = shift; a.bits = bits; a.out_cap = out_cap;
+    a.cursors = d_cursors; a.flag = d_flag; a.tile_counter = d_flag + 1;
+    a.peers = &peers;
+    HMJ_TRY(launch_scatter(ctx, a, ctas_per_sm, st));
+    hmj_prof_end_on(ctx, ev, st);
   }
-  HMJ_LAUNCHED(ctx);
-  hmj_prof_end(ctx, ev);
-  // hand my sub-region counts to the owners of the regions
   push_counts_kernel<<<((1u << bits) + 255) / 256, 256, 0, st>>>(d_cursors, 1u << bits, peers);
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 
-// Level 2 on this rank's own regions (`regions` of `cap1` slots, counts in cur1) -> padded
-// final buckets (bucket = (region << bits) | digit).
-int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
-                       uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
-                       uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag, int region_shift) {
-  cudaStream_t st = ctx->stream;
-  const uint32_t tile_items = bits > 8 ? 8192 : 4096;
-  const uint32_t tpr = (uint32_t)hmj_div_up(cap1, tile_items);
+// A local level on this rank's own regions (`regions` of `cap1` slots, counts in cur1) -> padded
+// buckets (bucket = ((region >> region_shift) << bits) | digit).
+int hmj_scatter_level2(hmj_ctx* ctx, cudaStream_t st, const uint64_t* k1, const uint32_t* v1,
+                       const uint32_t* cur1, uint32_t cap1, uint32_t regions, size_t n_hint, int shift,
+                       int bits, uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
+                       uint32_t* d_flag, uint32_t* d_tile_counter, int region_shift) {
   cudaEvent_t ev;
-  HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_SCATTER, (double)n_hint * 24.0, &ev));
-  if (bits > 8) {
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<1024, 1, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)UtCfg<1024>::SMEM));
-    bucket_scatter_tma_kernel<1024, 1, false><<<min(regions * tpr, (uint32_t)ctx->num_sms), 1024,
-                                                UtCfg<1024>::SMEM, st>>>(
-        k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits, cap_seg, cur2, d_flag,
-        hmj_peer_regions(), region_shift);
-  } else {
-    HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_tma_kernel<512, 2, false>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)UtCfg<512>::SMEM));
-    bucket_scatter_tma_kernel<512, 2, false><<<min(regions * tpr, (uint32_t)ctx->num_sms * 2), 512,
-                                               UtCfg<512>::SMEM, st>>>(
-        k1, v1, cur1, cap1, 0, tpr, regions * tpr, 0, k2, v2, shift, bits, cap_seg, cur2, d_flag,
-        hmj_peer_regions(), region_shift);
-  }
-  HMJ_LAUNCHED(ctx);
-  hmj_prof_end(ctx, ev);
+  HMJ_TRY(hmj_prof_begin_on(ctx, HMJ_K_SCATTER, (double)n_hint * 24.0, &ev, st));
+  ScatterLaunch a = {};
+  a.keys_in = k1; a.vals_in = v1; a.in_counts = cur1; a.in_stride = cap1;
+  a.tiles_per_region = (uint32_t)hmj_div_up(cap1, tile_items_for(bits));
+  a.total_tiles = regions * a.tiles_per_region;
+  a.keys_out = k2; a.vals_out = v2;
+  a.shift = shift; a.bits = bits; a.out_cap = cap_seg;
+  a.cursors = cur2; a.flag = d_flag; a.tile_counter = d_tile_counter;
+  a.region_shift = region_shift;
+  HMJ_TRY(launch_scatter(ctx, a, 0, st));
+  hmj_prof_end_on(ctx, ev, st);
   return HMJ_OK;
 }

@@ -133,7 +133,8 @@ static inline int hmj_ws(hmj_ctx* ctx, int slot, size_t count, T** out) {
 // Per-launch timing of the hot kernels while hmj_set_profiling is on: bracket a launch with
 //   cudaEvent_t after; HMJ_TRY(hmj_prof_begin(ctx, HMJ_K_x, bytes, &after)); <launch>; hmj_prof_end(ctx, after);
 // `bytes` = algorithmic bytes the launch moves.
-static inline int hmj_prof_begin(hmj_ctx* ctx, int kind, double bytes, cudaEvent_t* after) {
+static inline int hmj_prof_begin_on(hmj_ctx* ctx, int kind, double bytes, cudaEvent_t* after,
+                                    cudaStream_t st) {
   *after = nullptr;
   if (!ctx->prof_on) return HMJ_OK;
   if (ctx->prof_used + 2 > ctx->prof_events.size()) {
@@ -147,13 +148,19 @@ static inline int hmj_prof_begin(hmj_ctx* ctx, int kind, double bytes, cudaEvent
   }
   ctx->prof_kind[ctx->prof_used / 2] = kind;
   ctx->prof_bytes[ctx->prof_used / 2] = bytes;
-  HMJ_CUDA(ctx, cudaEventRecord(ctx->prof_events[ctx->prof_used], ctx->stream));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->prof_events[ctx->prof_used], st));
   *after = ctx->prof_events[ctx->prof_used + 1];
   ctx->prof_used += 2;
   return HMJ_OK;
 }
+static inline void hmj_prof_end_on(hmj_ctx* ctx, cudaEvent_t after, cudaStream_t st) {
+  if (after) cudaEventRecord(after, st);
+}
+static inline int hmj_prof_begin(hmj_ctx* ctx, int kind, double bytes, cudaEvent_t* after) {
+  return hmj_prof_begin_on(ctx, kind, bytes, after, ctx->stream);
+}
 static inline void hmj_prof_end(hmj_ctx* ctx, cudaEvent_t after) {
-  if (after) cudaEventRecord(after, ctx->stream);
+  hmj_prof_end_on(ctx, after, ctx->stream);
 }
 
 static inline size_t hmj_div_up(size_t a, size_t b) { return (a + b - 1) / b; }
@@ -178,13 +185,14 @@ struct hmj_peer_regions {
   int own_bits;         // log2(regions per GPU)
   int world, rank;      // GPUs of the job, this GPU
 };
-int hmj_scatter_level1_dist(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
-                            int shift, int bits, uint32_t out_cap, const hmj_peer_regions& peers,
-                            uint32_t* d_cursors, uint32_t* d_flag);
-int hmj_scatter_level2(hmj_ctx* ctx, const uint64_t* k1, const uint32_t* v1, const uint32_t* cur1,
-                       uint32_t cap1, uint32_t regions, size_t n_hint, int shift, int bits,
-                       uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag, int region_shift);
+int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_in, size_t n,
+                            uint32_t iota_base, int shift, int bits, uint32_t out_cap,
+                            const hmj_peer_regions& peers, uint32_t* d_cursors, uint32_t* d_flag,
+                            uint32_t ctas_per_sm);
+int hmj_scatter_level2(hmj_ctx* ctx, cudaStream_t st, const uint64_t* k1, const uint32_t* v1,
+                       const uint32_t* cur1, uint32_t cap1, uint32_t regions, size_t n_hint, int shift,
+                       int bits, uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
+                       uint32_t* d_flag, uint32_t* d_tile_counter, int region_shift);
 struct hmj_uniform_plan {
   int levels;        // 0 = not eligible
   int bits[2];

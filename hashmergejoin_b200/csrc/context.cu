@@ -66,6 +66,11 @@ extern "C" int hmj_release_workspace(hmj_ctx* ctx) {
     b.ptr = nullptr;
     b.bytes = 0;
   }
+  // the look-back descriptors are gone with WS_LOOKBACK: the next sort must clear its buffer even
+  // if cudaMalloc hands back the same address (stale words could carry a live epoch tag)
+  ctx->lb_seen_ptr = nullptr;
+  ctx->lb_seen_bytes = 0;
+  ctx->lb_epoch = 0;
   return HMJ_OK;
 }
 
@@ -148,6 +153,11 @@ int hmj_ws_get(hmj_ctx* ctx, int slot, size_t bytes, void** out) {
       HMJ_CUDA(ctx, cudaFree(b.ptr));
       b.ptr = nullptr;
       b.bytes = 0;
+      if (slot == WS_LOOKBACK) {
+        ctx->lb_seen_ptr = nullptr;
+        ctx->lb_seen_bytes = 0;
+        ctx->lb_epoch = 0;
+      }
     }
     size_t want = (bytes + 255) & ~size_t(255);
     HMJ_CUDA(ctx, cudaMalloc(&b.ptr, want));

@@ -1,4 +1,5 @@
-// dist_join.cu -- multi-GPU hash-merge join with the exchange FUSED into the first scatter level.
+// dist_join.cu -- multi-GPU hash-merge join with the exchange FUSED into the first scatter level
+// and the two relations PIPELINED against each other.
 //
 // every GPU splits its rows of R and S by hash range, one exchange moves range g
 // to GPU g, then every GPU joins its own range.  Here the split and the exchange are one kernel:
@@ -8,11 +9,25 @@
 // tile leaves as G runs of ~4096/G pairs: KBs per remote store).  Every source GPU owns a
 // sub-region of every destination (slot reservation = atomicAdd on a cursor in the SOURCE's
 // memory; the counts are handed to the owners after the kernel).  No partition pass, no send
-// buffers, no NCCL all-to-all; after a barrier every GPU cuts what it received on the bits below
-// in one or two local levels and runs the bucket join.  It stands in for partition_only's
-// per-thread push_back into shared partitions (partitioned_hash.h:82-124) at the scale of a node.
-// (First plan: level 1 cut on 9 bits, 512 regions spread over the GPUs -- runs of 16 pairs, 128-B
-// remote stores, ~300 GB/s of NVLink per GPU; C4 on 8 GPUs 13.4 ms.  GPU bits only: 10.0 ms.)
+// buffers, no NCCL all-to-all.  It stands in for partition_only's per-thread push_back into
+// shared partitions (partitioned_hash.h:82-124) at the scale of a node.
+//
+// One join is ONE call (hmj_dist_join_u64) that only enqueues work; the GPUs meet through flags in
+// each other's memory, not through host barriers:
+//   main stream  wait DONE(R, last join) -> level 1 of R over NVLink -> counts -> READY(R) to all
+//                wait DONE(S, last join) -> level 1 of S over NVLink -> counts -> READY(S) to all
+//                [after the side stream] wait READY(S) from all -> local levels of S -> DONE(S) to all
+//                -> bucket join
+//   side stream  wait READY(R) from all -> local levels of R -> DONE(R) to all
+// so the local levels of R (HBM-bound) run while S is still crossing NVLink.  READY(side) from
+// source s = "my runs and counts of this join are in your memory" (release store after the
+// kernels that wrote them; the owner acquires it in a one-CTA wait kernel in front of its local
+// level).  DONE(side) from owner o = "I have read your runs of this join": the source's next
+// level 1 waits for it before it overwrites them.  A wait gives up after HMJ_DIST_TIMEOUT_MS
+// (default 20000) and fails the join instead of hanging the GPU.
+// Level 1 of S is launched with one CTA per SM and the scatter kernels take their tiles from a
+// counter, so the local levels of R fill the other half of every SM while S is in flight and
+// all of it afterwards.
 //
 // One process per GPU: the regions are cudaMalloc'ed here and shared with CUDA IPC handles that
 // the caller exchanges over torch.distributed (hashmergejoin_b200/dist.py).
@@ -20,6 +35,49 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+
+namespace {
+constexpr int HANDLE_BYTES = 64;  // sizeof(cudaIpcMemHandle_t)
+static_assert(sizeof(cudaIpcMemHandle_t) == HANDLE_BYTES, "IPC handle size");
+constexpr int HANDLES_PER_RANK = 7;  // per side: keys, row ids, counts; then the signal words
+enum { SIG_READY = 0, SIG_DONE = 1 };
+// signal words of a rank: [kind][side][source or owner rank], 8 ranks at most
+__host__ __device__ inline int sig_slot(int kind, int side, int rank) { return (kind * 2 + side) * 8 + rank; }
+constexpr int SIG_WORDS = 64;
+
+struct sig_ptrs {
+  uint32_t* p[8];
+};
+
+// after the kernels that wrote into the peers' memory: tell every GPU of the job
+__global__ void dist_signal_kernel(const sig_ptrs sig, int world, int slot, uint32_t epoch) {
+  const int r = threadIdx.x;
+  if (r >= world) return;
+  __threadfence_system();
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sig.p[r] + slot), "r"(epoch) : "memory");
+}
+
+// in front of the kernels that read what the peers wrote: all `world` words at `mine` >= epoch
+__global__ void dist_wait_kernel(const uint32_t* mine, int world, uint32_t epoch,
+                                 uint32_t* fail_flag, unsigned long long timeout_ns) {
+  const int r = threadIdx.x;
+  if (r >= world) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine + r) : "memory");
+    if ((int32_t)(v - epoch) >= 0) break;
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) {
+      atomicOr(fail_flag, 4u);
+      break;
+    }
+    __nanosleep(100);
+  }
+}
+}  // namespace
 
 struct hmj_dist_state {
   int world = 1, rank = 0;
@@ -31,21 +89,27 @@ struct hmj_dist_state {
   uint64_t* k1[2] = {nullptr, nullptr};
   uint32_t* v1[2] = {nullptr, nullptr};
   uint32_t* c1[2] = {nullptr, nullptr};
-  // private: this source's cursors over all 2^b1 regions of the job (+ 8 words: [2^b1] = flag)
+  // private: this source's cursors over all 2^b1 regions of the job (+ 8 words: [2^b1] = flag,
+  // [2^b1 + 1] = tile counter of level 1)
   uint32_t* cur[2] = {nullptr, nullptr};
+  uint32_t* sig = nullptr;  // this rank's signal words (shared with the peers)
+  sig_ptrs sigs = {};
   hmj_peer_regions peers[2];
-  void* opened[2][8][3] = {};
+  void* opened[8][HANDLES_PER_RANK] = {};
   size_t rows_total = 0;
+  uint32_t epoch = 0;
+  cudaStream_t side_stream = nullptr;
+  cudaEvent_t ev_r_sent = nullptr, ev_r_local = nullptr;
+  unsigned long long timeout_ns = 20000ull * 1000000ull;
+  // what the last join moved (read back from the cursors and the owners' count tables)
+  uint64_t sent_pairs = 0, received_pairs[2] = {0, 0};
 };
 
-namespace {
-constexpr int HANDLE_BYTES = 64;  // sizeof(cudaIpcMemHandle_t)
-static_assert(sizeof(cudaIpcMemHandle_t) == HANDLE_BYTES, "IPC handle size");
-}  // namespace
+extern "C" int hmj_dist_handle_bytes(void) { return HANDLES_PER_RANK * HANDLE_BYTES; }
 
 // Plans the job for `rows_total` rows per relation over `world` GPUs, allocates this rank's
-// level-1 regions and writes their 6 IPC handles (R keys, R row ids, R cursors, S ...) to
-// handles_out[6 * 64].
+// level-1 regions and writes their 7 IPC handles (R keys, R row ids, R counts, S ..., signals)
+// to handles_out[hmj_dist_handle_bytes()].
 extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_total,
                               unsigned char* handles_out) {
   if (!ctx) return HMJ_EARG;
@@ -71,6 +135,10 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
     const int v = atoi(e);
     if (v > d->b1 && v <= 9 && v <= total_bits - 1) d->b1 = v;
   }
+  if (const char* e = getenv("HMJ_DIST_TIMEOUT_MS")) {
+    const long v = atol(e);
+    if (v > 0) d->timeout_ns = (unsigned long long)v * 1000000ull;
+  }
   const int rem = total_bits - d->b1;
   if (rem <= 9) {
     d->b2 = rem;
@@ -93,6 +161,10 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
   const double avg1 = (double)rows_total / (double)world / (double)(1u << d->b1);
   d->cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
   d->cap_seg = (uint32_t)hmj_segment_sort_cap();
+  ctx->dist = d;  // from here on hmj_dist_teardown frees what has been allocated
+  HMJ_CUDA(ctx, cudaStreamCreateWithFlags(&d->side_stream, cudaStreamNonBlocking));
+  HMJ_CUDA(ctx, cudaEventCreateWithFlags(&d->ev_r_sent, cudaEventDisableTiming));
+  HMJ_CUDA(ctx, cudaEventCreateWithFlags(&d->ev_r_local, cudaEventDisableTiming));
   for (int s = 0; s < 2; ++s) {
     const size_t subs = (size_t)d->regions_own * world;
     const size_t slots = subs * d->cap1;
@@ -108,11 +180,18 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
       memcpy(handles_out + (size_t)(s * 3 + j) * HANDLE_BYTES, &h, HANDLE_BYTES);
     }
   }
-  ctx->dist = d;
+  HMJ_CUDA(ctx, cudaMalloc(&d->sig, SIG_WORDS * 4));
+  HMJ_CUDA(ctx, cudaMemset(d->sig, 0, SIG_WORDS * 4));
+  {
+    cudaIpcMemHandle_t h;
+    HMJ_CUDA(ctx, cudaIpcGetMemHandle(&h, d->sig));
+    memcpy(handles_out + (size_t)6 * HANDLE_BYTES, &h, HANDLE_BYTES);
+  }
+  HMJ_CUDA(ctx, cudaDeviceSynchronize());  // the memsets have landed before any peer writes here
   return HMJ_OK;
 }
 
-// all_handles[world][6][64]: what every rank wrote in hmj_dist_setup, in rank order.
+// all_handles[world][7][64]: what every rank wrote in hmj_dist_setup, in rank order.
 extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) {
   if (!ctx) return HMJ_EARG;
   HMJ_ARG(ctx, ctx->dist != nullptr && all_handles != nullptr);
@@ -123,105 +202,194 @@ extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) 
     d->peers[s].own_bits = d->own_bits;
     d->peers[s].world = d->world;
     d->peers[s].rank = d->rank;
-    for (int r = 0; r < d->world; ++r) {
-      void* ptrs[3];
-      if (r == d->rank) {
-        ptrs[0] = d->k1[s]; ptrs[1] = d->v1[s]; ptrs[2] = d->c1[s];
-      } else {
-        for (int j = 0; j < 3; ++j) {
-          cudaIpcMemHandle_t h;
-          memcpy(&h, all_handles + ((size_t)r * 6 + s * 3 + j) * HANDLE_BYTES, HANDLE_BYTES);
-          HMJ_CUDA(ctx, cudaIpcOpenMemHandle(&ptrs[j], h, cudaIpcMemLazyEnablePeerAccess));
-          d->opened[s][r][j] = ptrs[j];
-        }
+  }
+  for (int r = 0; r < d->world; ++r) {
+    void* ptrs[HANDLES_PER_RANK];
+    if (r == d->rank) {
+      for (int s = 0; s < 2; ++s) {
+        ptrs[s * 3 + 0] = d->k1[s]; ptrs[s * 3 + 1] = d->v1[s]; ptrs[s * 3 + 2] = d->c1[s];
       }
-      d->peers[s].keys[r] = reinterpret_cast<uint64_t*>(ptrs[0]);
-      d->peers[s].vals[r] = reinterpret_cast<uint32_t*>(ptrs[1]);
-      d->peers[s].counts[r] = reinterpret_cast<uint32_t*>(ptrs[2]);
+      ptrs[6] = d->sig;
+    } else {
+      for (int j = 0; j < HANDLES_PER_RANK; ++j) {
+        cudaIpcMemHandle_t h;
+        memcpy(&h, all_handles + ((size_t)r * HANDLES_PER_RANK + j) * HANDLE_BYTES, HANDLE_BYTES);
+        HMJ_CUDA(ctx, cudaIpcOpenMemHandle(&ptrs[j], h, cudaIpcMemLazyEnablePeerAccess));
+        d->opened[r][j] = ptrs[j];
+      }
     }
+    for (int s = 0; s < 2; ++s) {
+      d->peers[s].keys[r] = reinterpret_cast<uint64_t*>(ptrs[s * 3 + 0]);
+      d->peers[s].vals[r] = reinterpret_cast<uint32_t*>(ptrs[s * 3 + 1]);
+      d->peers[s].counts[r] = reinterpret_cast<uint32_t*>(ptrs[s * 3 + 2]);
+    }
+    d->sigs.p[r] = reinterpret_cast<uint32_t*>(ptrs[6]);
   }
   return HMJ_OK;
 }
 
-// Zeroes this rank's cursors and flags (private to the rank: no barrier is needed before the
-// scatter; the one after it publishes runs and counts to their owners).
-extern "C" int hmj_dist_begin(hmj_ctx* ctx) {
+namespace {
+
+int dist_signal(hmj_ctx* ctx, cudaStream_t st, int kind, int side) {
+  hmj_dist_state* d = ctx->dist;
+  dist_signal_kernel<<<1, 32, 0, st>>>(d->sigs, d->world, sig_slot(kind, side, d->rank), d->epoch);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
+}
+
+int dist_wait(hmj_ctx* ctx, cudaStream_t st, int kind, int side, uint32_t epoch) {
+  hmj_dist_state* d = ctx->dist;
+  uint32_t* fail = d->cur[side] + ((size_t)1 << d->b1);
+  dist_wait_kernel<<<1, 32, 0, st>>>(d->sig + sig_slot(kind, side, 0), d->world, epoch, fail,
+                                     d->timeout_ns);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
+}
+
+// local levels of `side` on this rank's hash range -> padded final buckets
+int dist_local_levels(hmj_ctx* ctx, cudaStream_t st, int s, hmj_uniform_buckets* out) {
+  hmj_dist_state* d = ctx->dist;
+  const uint32_t regions2 = d->regions_own << d->b2;  // after the first local level
+  const uint32_t buckets = regions2 << d->b3;         // final
+  const size_t n_hint = d->rows_total / d->world;
+  // scratch words: [8: tile counters at 1, 2][final cursors: buckets][middle cursors: regions2]
+  uint32_t* words = reinterpret_cast<uint32_t*>(ctx->ws[s ? WS_US_CURSORS_1 : WS_US_CURSORS].ptr);
+  const size_t nwords = (size_t)8 + buckets + (d->b3 ? regions2 : 0);
+  HMJ_TRY(hmj_fill_async(ctx, words, 0, nwords * 4, st));
+  uint64_t* k2 = reinterpret_cast<uint64_t*>(ctx->ws[s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B].ptr);
+  uint32_t* v2 = reinterpret_cast<uint32_t*>(ctx->ws[s ? WS_SORT_VALS_C : WS_SORT_VALS_B].ptr);
+  uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);  // this rank's level-1 overflows land here too
+  const uint32_t subs = d->regions_own * (uint32_t)d->world;
+  if (d->b3 == 0) {
+    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
+                               64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag,
+                               words + 1, d->g_bits));
+    HMJ_TRY(dist_signal(ctx, st, SIG_DONE, s));
+  } else {
+    // sub-regions -> regions2 middle regions (one buffer, used by R then by S) -> final buckets
+    uint64_t* km = reinterpret_cast<uint64_t*>(ctx->ws[WS_SORT_KEYS_A].ptr);
+    uint32_t* vm = reinterpret_cast<uint32_t*>(ctx->ws[WS_SORT_VALS_A].ptr);
+    uint32_t* cur_mid = words + 8 + buckets;
+    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
+                               64 - d->b1 - d->b2, d->b2, km, vm, d->cap2, cur_mid, flag, words + 1,
+                               d->g_bits));
+    HMJ_TRY(dist_signal(ctx, st, SIG_DONE, s));
+    HMJ_TRY(hmj_scatter_level2(ctx, st, km, vm, cur_mid, d->cap2, regions2, n_hint,
+                               64 - d->b1 - d->b2 - d->b3, d->b3, k2, v2, d->cap_seg, words + 8, flag,
+                               words + 2, 0));
+  }
+  out->keys = k2;
+  out->vals = v2;
+  out->counts = words + 8;
+  out->offsets = nullptr;
+  out->flag = flag;
+  out->buckets = buckets;
+  return HMJ_OK;
+}
+
+}  // namespace
+
+// The whole multi-GPU join of this rank's blocks of R and S (global row ids r_rowid_base + i and
+// s_rowid_base + i).  Every rank of the job calls it once per join, in the same order; nothing
+// else synchronises the ranks.  *ok = 0: a region or bucket overflowed on this rank, or a peer did
+// not answer in time (the caller agrees on that across ranks and takes the NCCL path).  On
+// success this rank's pairs (its hash range) are in the context's result buffers.
+extern "C" int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
+                                 uint32_t r_rowid_base, const uint64_t* d_skeys, size_t ns,
+                                 uint32_t s_rowid_base, uint64_t* h_num_pairs, int* ok) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, ctx->dist != nullptr && h_num_pairs && ok);
+  HMJ_ARG(ctx, (nr == 0 || d_rkeys) && (ns == 0 || d_skeys));
+  HMJ_ARG(ctx, ((reinterpret_cast<uintptr_t>(d_rkeys) | reinterpret_cast<uintptr_t>(d_skeys)) & 15) == 0);
+  hmj_dist_state* d = ctx->dist;
+  HMJ_ARG(ctx, d->sigs.p[d->rank] != nullptr);  // hmj_dist_connect has run
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream, st2 = d->side_stream;
+  *ok = 0;
+  *h_num_pairs = 0;
+  ctx->tm.sort_passes = ctx->tm.sort_finishes = ctx->tm.sort_fallbacks = ctx->tm.sort_uniform = 0;
+  ctx->tm.bucket_join = 0;
+  ctx->tm.scatter_levels = 0;
+
+  // every buffer of the join, before anything is enqueued (growing one synchronises the stream)
+  const uint32_t regions2 = d->regions_own << d->b2, buckets = regions2 << d->b3;
+  for (int s = 0; s < 2; ++s) {
+    void* p = nullptr;
+    HMJ_TRY(hmj_ws_get(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS,
+                       ((size_t)8 + buckets + (d->b3 ? regions2 : 0)) * 4, &p));
+    HMJ_TRY(hmj_ws_get(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, (size_t)buckets * d->cap_seg * 8, &p));
+    HMJ_TRY(hmj_ws_get(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, (size_t)buckets * d->cap_seg * 4, &p));
+  }
+  if (d->b3) {
+    void* p = nullptr;
+    HMJ_TRY(hmj_ws_get(ctx, WS_SORT_KEYS_A, (size_t)regions2 * d->cap2 * 8, &p));
+    HMJ_TRY(hmj_ws_get(ctx, WS_SORT_VALS_A, (size_t)regions2 * d->cap2 * 4, &p));
+  }
+
+  const uint32_t epoch = ++d->epoch;
+  const size_t cur_words = ((size_t)1 << d->b1) + 8;
+  enum { EV_START = 0, EV_HASHED, EV_SORTED, EV_JOINED };
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], st));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], st));  // identity hash: no kernel
+  for (int s = 0; s < 2; ++s) HMJ_TRY(hmj_fill_async(ctx, d->cur[s], 0, cur_words * 4, st));
+
+  // R crosses NVLink
+  HMJ_TRY(dist_wait(ctx, st, SIG_DONE, 0, epoch - 1));
+  HMJ_TRY(hmj_scatter_level1_dist(ctx, st, d_rkeys, nr, r_rowid_base, 64 - d->b1, d->b1, d->cap1,
+                                  d->peers[0], d->cur[0], d->cur[0] + ((size_t)1 << d->b1), 0));
+  HMJ_TRY(dist_signal(ctx, st, SIG_READY, 0));
+  HMJ_CUDA(ctx, cudaEventRecord(d->ev_r_sent, st));
+  // side stream: R's local levels as soon as every source's runs are here
+  hmj_uniform_buckets B[2];
+  HMJ_CUDA(ctx, cudaStreamWaitEvent(st2, d->ev_r_sent, 0));
+  HMJ_TRY(dist_wait(ctx, st2, SIG_READY, 0, epoch));
+  HMJ_TRY(dist_local_levels(ctx, st2, 0, &B[0]));
+  HMJ_CUDA(ctx, cudaEventRecord(d->ev_r_local, st2));
+  // S crosses NVLink meanwhile (one CTA per SM: the other half of every SM is R's)
+  HMJ_TRY(dist_wait(ctx, st, SIG_DONE, 1, epoch - 1));
+  const char* e1 = getenv("HMJ_DIST_S_CTAS");
+  HMJ_TRY(hmj_scatter_level1_dist(ctx, st, d_skeys, ns, s_rowid_base, 64 - d->b1, d->b1, d->cap1,
+                                  d->peers[1], d->cur[1], d->cur[1] + ((size_t)1 << d->b1),
+                                  e1 ? (uint32_t)atoi(e1) : 1u));
+  HMJ_TRY(dist_signal(ctx, st, SIG_READY, 1));
+  HMJ_CUDA(ctx, cudaStreamWaitEvent(st, d->ev_r_local, 0));
+  HMJ_TRY(dist_wait(ctx, st, SIG_READY, 1, epoch));
+  HMJ_TRY(dist_local_levels(ctx, st, 1, &B[1]));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], st));
+
+  const size_t n_hint = d->rows_total / d->world;
+  HMJ_TRY(hmj_bucket_join_run(ctx, HMJ_KEY_U64, B[0], B[1], d->cap_seg,
+                              64 - d->b1 - d->b2 - d->b3 - 12, n_hint, n_hint, nullptr, nullptr,
+                              nullptr, nullptr, h_num_pairs, ok));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], st));
+  if (*ok) ctx->tm.bucket_join = 1;
+  return HMJ_OK;
+}
+
+// What the last hmj_dist_join_u64 moved, read back from the device: pairs this rank wrote into
+// OTHER ranks' memory (level-1 cursors of the regions it does not own, both relations) and the
+// pairs of R and of S it received (the owners' count tables).  Synchronises the stream.
+extern "C" int hmj_dist_last_exchange(hmj_ctx* ctx, uint64_t* sent_pairs_remote,
+                                      uint64_t* received_r, uint64_t* received_s) {
   if (!ctx) return HMJ_EARG;
   HMJ_ARG(ctx, ctx->dist != nullptr);
   hmj_dist_state* d = ctx->dist;
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
-  for (int s = 0; s < 2; ++s)
-    HMJ_TRY(hmj_fill_async(ctx, d->cur[s], 0, (((size_t)1 << d->b1) + 8) * 4, ctx->stream));
-  return HMJ_OK;
-}
-
-// Level 1 over this rank's rows of relation `side` (global row ids rowid_base + i), written into
-// the regions of all ranks.  Returns after the kernel has completed (its peer writes are then
-// visible to their owners once the caller's barrier has passed).
-extern "C" int hmj_dist_scatter(hmj_ctx* ctx, int side, const uint64_t* d_keys, size_t n,
-                                uint32_t rowid_base) {
-  if (!ctx) return HMJ_EARG;
-  HMJ_ARG(ctx, ctx->dist != nullptr && (side == 0 || side == 1) && (n == 0 || d_keys));
-  hmj_dist_state* d = ctx->dist;
-  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
-  uint32_t* flag = d->cur[side] + ((size_t)1 << d->b1);
-  HMJ_TRY(hmj_scatter_level1_dist(ctx, d_keys, n, rowid_base, 64 - d->b1, d->b1, d->cap1,
-                                  d->peers[side], d->cur[side], flag));
   HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  return HMJ_OK;
-}
-
-// Level 2 + bucket join on this rank's hash range.  *ok = 0: some region or bucket overflowed on
-// this rank (the caller agrees on that across ranks and falls back to the NCCL path).
-extern "C" int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok) {
-  if (!ctx) return HMJ_EARG;
-  HMJ_ARG(ctx, ctx->dist != nullptr && h_num_pairs && ok);
-  hmj_dist_state* d = ctx->dist;
-  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  *ok = 0;
-  *h_num_pairs = 0;
-  const uint32_t regions2 = d->regions_own << d->b2;        // after the first local level
-  const uint32_t buckets = regions2 << d->b3;               // final
-  const size_t n_hint = d->rows_total / d->world;
-  hmj_uniform_buckets B[2];
+  const size_t regions = (size_t)1 << d->b1, subs = (size_t)d->regions_own * d->world;
+  std::vector<uint32_t> h(regions > subs ? regions : subs);
+  uint64_t sent = 0, recv[2] = {0, 0};
   for (int s = 0; s < 2; ++s) {
-    // scratch words: [8 spare][final cursors: buckets][middle cursors: regions2]
-    uint32_t* words = nullptr;
-    const size_t nwords = (size_t)8 + buckets + (d->b3 ? regions2 : 0);
-    HMJ_TRY(hmj_ws(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, nwords, &words));
-    HMJ_TRY(hmj_fill_async(ctx, words, 0, nwords * 4, st));
-    uint64_t* k2 = nullptr;
-    uint32_t* v2 = nullptr;
-    const size_t slots2 = (size_t)buckets * d->cap_seg;
-    HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, slots2, &k2));
-    HMJ_TRY(hmj_ws(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, slots2, &v2));
-    uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);  // this rank's level-1 overflows land here too
-    const uint32_t subs = d->regions_own * (uint32_t)d->world;
-    if (d->b3 == 0) {
-      HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
-                                 64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag, d->g_bits));
-    } else {
-      // sub-regions -> regions2 middle regions (one buffer, used by R then by S) -> final buckets
-      uint64_t* km = nullptr;
-      uint32_t* vm = nullptr;
-      uint32_t* cur_mid = words + 8 + buckets;
-      HMJ_TRY(hmj_ws(ctx, WS_SORT_KEYS_A, (size_t)regions2 * d->cap2, &km));
-      HMJ_TRY(hmj_ws(ctx, WS_SORT_VALS_A, (size_t)regions2 * d->cap2, &vm));
-      HMJ_TRY(hmj_scatter_level2(ctx, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
-                                 64 - d->b1 - d->b2, d->b2, km, vm, d->cap2, cur_mid, flag, d->g_bits));
-      HMJ_TRY(hmj_scatter_level2(ctx, km, vm, cur_mid, d->cap2, regions2, n_hint,
-                                 64 - d->b1 - d->b2 - d->b3, d->b3, k2, v2, d->cap_seg, words + 8, flag, 0));
-    }
-    B[s].keys = k2;
-    B[s].vals = v2;
-    B[s].counts = words + 8;
-    B[s].offsets = nullptr;
-    B[s].flag = flag;
-    B[s].buckets = buckets;
+    HMJ_CUDA(ctx, cudaMemcpy(h.data(), d->cur[s], regions * 4, cudaMemcpyDeviceToHost));
+    for (size_t r = 0; r < regions; ++r)
+      if ((int)(r >> d->own_bits) != d->rank) sent += h[r];
+    HMJ_CUDA(ctx, cudaMemcpy(h.data(), d->c1[s], subs * 4, cudaMemcpyDeviceToHost));
+    for (size_t r = 0; r < subs; ++r) recv[s] += h[r];
   }
-  return hmj_bucket_join_run(ctx, HMJ_KEY_U64, B[0], B[1], d->cap_seg, 64 - d->b1 - d->b2 - d->b3 - 12,
-                             n_hint, n_hint, nullptr, nullptr, nullptr, nullptr, h_num_pairs, ok);
+  if (sent_pairs_remote) *sent_pairs_remote = sent;
+  if (received_r) *received_r = recv[0];
+  if (received_s) *received_s = recv[1];
+  return HMJ_OK;
 }
 
 extern "C" int hmj_dist_teardown(hmj_ctx* ctx) {
@@ -230,16 +398,24 @@ extern "C" int hmj_dist_teardown(hmj_ctx* ctx) {
   if (!d) return HMJ_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  if (d->side_stream) {
+    cudaStreamSynchronize(d->side_stream);
+    cudaStreamDestroy(d->side_stream);
+  }
+  if (d->ev_r_sent) cudaEventDestroy(d->ev_r_sent);
+  if (d->ev_r_local) cudaEventDestroy(d->ev_r_local);
+  for (int r = 0; r < 8; ++r)
+    for (int j = 0; j < HANDLES_PER_RANK; ++j)
+      if (d->opened[r][j]) cudaIpcCloseMemHandle(d->opened[r][j]);
   for (int s = 0; s < 2; ++s) {
-    for (int r = 0; r < 8; ++r)
-      for (int j = 0; j < 3; ++j)
-        if (d->opened[s][r][j]) cudaIpcCloseMemHandle(d->opened[s][r][j]);
     if (d->k1[s]) cudaFree(d->k1[s]);
     if (d->v1[s]) cudaFree(d->v1[s]);
     if (d->c1[s]) cudaFree(d->c1[s]);
     if (d->cur[s]) cudaFree(d->cur[s]);
   }
+  if (d->sig) cudaFree(d->sig);
   delete d;
   ctx->dist = nullptr;
+  cudaGetLastError();
   return HMJ_OK;
 }

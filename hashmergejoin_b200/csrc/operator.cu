@@ -32,6 +32,8 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   ctx->tm.sort_finishes = 0;
   ctx->tm.sort_fallbacks = 0;
   ctx->tm.sort_uniform = 0;
+  ctx->tm.bucket_join = 0;
+  ctx->tm.scatter_levels = 0;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));  // identity hash: no kernel
   {
@@ -40,7 +42,7 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
     HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_U64, d_rkeys, nullptr, nr, d_skeys, nullptr, ns, 0, nullptr, nullptr,
                                  nullptr, nullptr, ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
-      ctx->tm.sort_uniform += 2;
+      ctx->tm.bucket_join = 1;
       HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
       return HMJ_OK;
     }
@@ -69,6 +71,8 @@ extern "C" int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint3
   ctx->tm.sort_finishes = 0;
   ctx->tm.sort_fallbacks = 0;
   ctx->tm.sort_uniform = 0;
+  ctx->tm.bucket_join = 0;
+  ctx->tm.scatter_levels = 0;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], ctx->stream));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], ctx->stream));
   {
@@ -77,7 +81,7 @@ extern "C" int hmj_join_pairs(hmj_ctx* ctx, const uint64_t* d_rhash, const uint3
                                  prefix_bits, nullptr, nullptr, nullptr, nullptr,
                                  ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
-      ctx->tm.sort_uniform += 2;
+      ctx->tm.bucket_join = 1;
       HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
       return HMJ_OK;
     }
@@ -117,6 +121,8 @@ extern "C" int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, 
   ctx->tm.sort_finishes = 0;
   ctx->tm.sort_fallbacks = 0;
   ctx->tm.sort_uniform = 0;
+  ctx->tm.bucket_join = 0;
+  ctx->tm.scatter_levels = 0;
   uint64_t *rh = nullptr, *sh = nullptr;
   uint32_t *rr = nullptr, *sr = nullptr;
   HMJ_TRY(hmj_ws(ctx, WS_R_HASH, nr, &rh));
@@ -135,7 +141,7 @@ extern "C" int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, 
     HMJ_TRY(hmj_join_uniform_try(ctx, HMJ_KEY_STRING, rt, nullptr, nr, st, nullptr, ns, prefix_bits, d_roffsets, d_rchars,
                                  d_soffsets, d_schars, ctx->ev[EV_SORTED], h_num_pairs, &ok));
     if (ok) {
-      ctx->tm.sort_uniform += 2;
+      ctx->tm.bucket_join = 1;
       HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], ctx->stream));
       return HMJ_OK;
     }

@@ -136,6 +136,98 @@ def zipf_indices(n_draws, n_keys, s=1.0, seed=7):
     return np.minimum(np.searchsorted(cdf, u), n_keys - 1).astype(np.int64)
 
 
+# ---- numpy restatements of the device generators in csrc/datagen.cu ----------------------
+def _fmix32(h):
+    h = h.astype(np.uint32)
+    h ^= h >> np.uint32(16)
+    h = (h.astype(np.uint64) * np.uint64(0x85EBCA6B)).astype(np.uint32)
+    h ^= h >> np.uint32(13)
+    h = (h.astype(np.uint64) * np.uint64(0xC2B2AE35)).astype(np.uint32)
+    h ^= h >> np.uint32(16)
+    return h
+
+
+def feistel_permute(x, domain, seed):
+    """hmj_gen_permute: a seeded bijection of [0, domain) applied to the uint32 array x
+    (4-round balanced Feistel network on the next even number of bits, cycle-walked)."""
+    half_bits = 1
+    while half_bits < 16 and (1 << (2 * half_bits)) < domain:
+        half_bits += 1
+    hm = np.uint32((1 << half_bits) - 1)
+    x = np.asarray(x, dtype=np.uint32).copy()
+    todo = np.ones(x.shape, bool)
+    while todo.any():
+        v = x[todo]
+        l, r = v >> np.uint32(half_bits), v & hm
+        for rnd in range(4):
+            key = np.uint32((seed + rnd * 0x9E3779B9) & 0xFFFFFFFF)
+            f = _fmix32(r ^ key) & hm
+            l, r = r, l ^ f
+        v = (l << np.uint32(half_bits)) | r
+        x[todo] = v
+        todo[todo] = v >= domain
+    return x
+
+
+def zipf_cdf(n_keys, s=1.0):
+    """float64 prefix table of P(k) ~ 1/(k+1)^s, last entry exactly 1.0"""
+    w = 1.0 / np.power(np.arange(1, n_keys + 1, dtype=np.float64), s)
+    cdf = np.cumsum(w)
+    cdf /= cdf[-1]
+    cdf[-1] = 1.0
+    return cdf
+
+
+def zipf_ranks(cdf, n, seed, row_base=0):
+    """hmj_gen_zipf: rank of row i = first k with cdf[k] > u(seed, row_base + i)"""
+    with np.errstate(over="ignore"):
+        ctr = np.uint64(seed) * np.uint64(0xD1342543DE82EF95) + np.uint64(row_base) + np.arange(n, dtype=np.uint64)
+    u = (splitmix64(ctr) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+    return np.minimum(np.searchsorted(cdf, u, side="right"), cdf.size - 1).astype(np.uint32)
+
+
+def strgen_keys(woff, wchars, key_ids):
+    """hmj_gen_strgen_*: (offsets, chars) of the strgen keys `key_ids` over the word table:
+    id < q is word id, otherwise word_i + "-" + word_j with (i, j) = divmod(id - q, q)."""
+    q = woff.size - 1
+    out = []
+    for k in np.asarray(key_ids, dtype=np.int64):
+        w = lambda i: bytes(wchars[int(woff[i]):int(woff[i + 1])])
+        out.append(w(k) if k < q else w((k - q) // q) + b"-" + w((k - q) % q))
+    return strings_from_list(out)
+
+
+class DeviceStrgen:
+    """strgen-shaped relations generated in HBM (csrc/datagen.cu) over `n_keys` distinct keys:
+    the word table is the host's seeded synthetic list (word_list), everything per row runs on
+    the GPU.  Relations are described by a key id per row."""
+
+    def __init__(self, ctx, n_keys, seed=1234):
+        import torch
+        self.ctx, self.n_keys = ctx, n_keys
+        self.q = int(math.ceil(math.sqrt(n_keys)))
+        woff, wchars = word_list(self.q, seed)
+        self.h_woff, self.h_wchars = woff, wchars
+        self.woff = torch.from_numpy(woff.view(np.int64)).to(ctx.device)
+        self.wchars = torch.from_numpy(wchars).to(ctx.device)
+
+    def shuffled_ids(self, n_rows, seed, copies=1, row_base=0):
+        """key ids of rows [row_base, row_base + n_rows) of a relation holding every key `copies`
+        times in a seeded random order (copies = 1: create_strvec's shuffle)"""
+        ids = self.ctx.gen_permute(n_rows, self.n_keys * copies, seed, base=row_base)
+        if copies > 1:
+            ids = (ids // copies).to(ids.dtype)   # values < 2^31: plain integer division
+        return ids
+
+    def zipf_ids(self, cdf, n_rows, seed, key_seed, row_base=0):
+        """Zipf-distributed key ids: rank k -> key P(k), so that the hot keys are arbitrary ones"""
+        ranks = self.ctx.gen_zipf(cdf, n_rows, seed, row_base)
+        return self.ctx.gen_permute(n_rows, self.n_keys, key_seed, src=ranks)
+
+    def keys(self, ids):
+        return self.ctx.gen_strgen(self.woff, self.wchars, ids)
+
+
 # ---- device-side generators (torch; harness only) for the full-size configurations -------
 def _lsr(x, s):
     """logical shift right on int64 tensors (torch's >> is arithmetic)"""

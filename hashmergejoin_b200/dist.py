@@ -16,6 +16,7 @@ import os
 import torch
 import torch.distributed as dist
 
+from ._lib import HmjError
 from .api import SortedRelation
 
 
@@ -87,15 +88,21 @@ def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, wor
 
 
 class DistJoin:
+    """One per rank.  join_u64 / join_strings are collective: every rank of the job calls them in
+    the same order.  With ``rows_total_hint`` and the NCCL backend the integer-key join runs the
+    fused path (hmj_dist_join_u64: level 1 of the bucket scatter writes into the owners' memory
+    over NVLink, relations pipelined, no host barrier); otherwise, and whenever a region overflows
+    (skewed keys), the NCCL path: stable partition pass + all_to_all_single + local join."""
+
     def __init__(self, ctx, rank, world, rows_total_hint=0):
         self.ctx, self.rank, self.world = ctx, rank, world
         self.bits = partition_bits(world)
-        self.exchange_bytes = 0      # bytes this rank sent over NVLink in the last join
+        self.exchange_bytes = 0      # bytes this rank sent to OTHER ranks in the last join
+        self.exchange_measured = False  # read back from the device cursors (fused path), not a formula
         self.local_rows = (0, 0)     # (|R|, |S|) of this rank's hash range in the last join
-        # fused path: level 1 of the bucket scatter writes straight into the owners' regions over
-        # NVLink peer memory (CUDA IPC handles exchanged here); needs the job size up front
         self.fused = False
         self.fused_joins = 0
+        self.fallback_joins = 0
         if world > 1 and rows_total_hint > 0 and dist.get_backend() == "nccl" \
                 and os.environ.get("HMJ_DIST_FUSED", "1") != "0":
             try:
@@ -110,6 +117,14 @@ class DistJoin:
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             self.fused = bool(flag.item())
 
+    def close(self):
+        """Collective: no rank may free its regions while another still writes into them."""
+        if self.fused:
+            torch.cuda.synchronize()
+            dist.barrier()
+            self.ctx.dist_teardown()
+            self.fused = False
+
     def _exchange_side(self, keys, rowid_base):
         """partition local rows by destination, exchange -> (hash, rowid) tensors of my range"""
         ctx, G = self.ctx, self.world
@@ -123,30 +138,48 @@ class DistJoin:
         self.exchange_bytes += 12 * (sum(mat[self.rank]) - mat[self.rank][self.rank])
         return rh, rr
 
-    def join_u64(self, rkeys_local, skeys_local, want_pairs=False):
-        """Returns the number of pairs this rank produced (its hash range)."""
+    def join_u64(self, rkeys_local, skeys_local, want_pairs=False, measure_exchange=False):
+        """Returns the number of pairs this rank produced (its hash range).  Global row ids are
+        rank-major blocks: rank r owns rows [r*n, (r+1)*n) of a relation, so every rank must pass
+        blocks of the same size (checked across ranks on the fused path)."""
         ctx = self.ctx
         nr, ns = rkeys_local.numel(), skeys_local.numel()
         self.exchange_bytes = 0
+        self.exchange_measured = False
         if self.fused and not want_pairs:
-            ctx.dist_begin()
-            dist.barrier()
-            ctx.dist_scatter(0, rkeys_local, self.rank * nr)
-            ctx.dist_scatter(1, skeys_local, self.rank * ns)
-            dist.barrier()
-            m, ok = ctx.dist_join()
-            t = torch.tensor([ok], device=rkeys_local.device)
+            # a rank that cannot even start (bad argument) must not leave the others waiting for
+            # its flags until they time out: it reports not-ok and everybody takes the NCCL path
+            m, ok, err = 0, 0, None
+            try:
+                m, ok = ctx.dist_join_u64(rkeys_local, self.rank * nr, skeys_local, self.rank * ns)
+            except Exception as e:
+                err = e
+            # one small all-reduce: everybody ok?  same block sizes everywhere?
+            t = torch.tensor([ok, nr, -nr, ns, -ns], dtype=torch.int64, device=rkeys_local.device)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
-            if int(t.item()) == 1:
+            t = t.tolist()
+            if t[1] != -t[2] or t[3] != -t[4]:
+                raise ValueError("DistJoin.join_u64: ranks passed blocks of different sizes "
+                                 "(global row ids are rank * block size)")
+            if t[0] == 1:
                 self.fused_joins += 1
-                # uniform hashes: (G-1)/G of the local rows leave the rank, 12 B per pair
-                self.exchange_bytes = 12 * (nr + ns) * (self.world - 1) // self.world
-                self.local_rows = (nr, ns)
+                if measure_exchange:
+                    sent, got_r, got_s = ctx.dist_last_exchange()
+                    self.exchange_bytes, self.exchange_measured = 12 * sent, True
+                    self.local_rows = (got_r, got_s)
+                else:
+                    # uniform hashes: (G-1)/G of the local rows leave the rank, 12 B per pair
+                    self.exchange_bytes = 12 * (nr + ns) * (self.world - 1) // self.world
+                    self.local_rows = (nr, ns)
                 return m
+            self.fallback_joins += 1
+            if err is not None and not isinstance(err, HmjError):
+                raise err
         # global row ids: rank-major blocks (rank r owns rows [r*n, (r+1)*n) of each relation)
         rh, rr = self._exchange_side(rkeys_local, self.rank * nr)
         sh, sr = self._exchange_side(skeys_local, self.rank * ns)
         self.local_rows = (rh.numel(), sh.numel())
+        self.exchange_measured = True
         if want_pairs:
             # staged API (tests: sorted ranges of the ranks concatenate to the global sorted array)
             rh, rr = ctx.sort_pairs(rh, rr, out_hash=rh, out_rowid=rr)

@@ -120,8 +120,16 @@ int hmj_merge_join_aggregate(hmj_ctx* ctx, const hmj_relation* r, const hmj_rela
 
 /* ---- whole operator: HashMergeJoin(r_begin,r_end,s_begin,s_end) ----------------------- */
 /* replaces HashMergeJoin ctor + full iteration (hashjoin.h:56-68,183-195) with DEVICE inputs.
- * Hash both sides, sort both, merge-join; the result stays in context-owned device buffers
- * until the next join on this context.  *h_num_pairs receives the pair count. */
+ * Same result multiset as hash -> sort -> merge walk.  Two plans, chosen by the library:
+ *  (a) radix-partition + in-shared-memory bucket join: both sides are cut on the same top hash
+ *      bits (bucket_scatter.cu), every bucket pair is joined in shared memory (bucket_join.cu);
+ *      nothing is sorted or merged.  Runs when the hashes spread evenly (hmj_timings.bucket_join
+ *      = 1).  Pair order: bucket arrival order (unspecified; HMJ_JOIN_ORDER=hash gives ascending
+ *      bucket order, deterministic between runs).
+ *  (b) onesweep sort of both sides + merge-path join (radix_sort.cu, merge_join.cu) for skewed
+ *      or heavily duplicated hashes; pairs come in ascending hash order.
+ * The result stays in context-owned device buffers until the next join on this context.
+ * *h_num_pairs receives the pair count. */
 int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr, const uint64_t* d_skeys,
                  size_t ns, uint64_t* h_num_pairs);
 /* The local step of the multi-GPU join: two UNSORTED relations of (hash, global
@@ -201,19 +209,47 @@ int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r_unsorted,
                              const uint64_t* d_svals, uint64_t* h_hits, uint64_t* h_sum);
 
 /* ---- multi-GPU join with the exchange fused into the first scatter level (dist_join.cu) --
- * One process per GPU.  setup: plan for rows_total rows per relation over `world` GPUs (power of
- * two, <= 8), allocate this rank's level-1 regions, export their 6 CUDA IPC handles (6 x 64
- * bytes).  connect: all ranks' handles in rank order (world x 6 x 64 bytes).  Per join:
- * begin (zero own cursors) -> BARRIER -> scatter(side 0 = R, 1 = S: level 1 over the local rows,
- * runs written into the owners' memory over NVLink) -> BARRIER -> join (level 2 + bucket join of
- * the own hash range; *ok = 0 when a region overflowed: every rank then uses the NCCL path).
- * Replaces partition_only's shared partitions (partitioned_hash.h:82-124) at node scale. */
+ * One process per GPU.  Replaces partition_only's shared partitions (partitioned_hash.h:82-124)
+ * at node scale.
+ * setup: plan for rows_total rows per relation over `world` GPUs (power of two, <= 8), allocate
+ *   this rank's level-1 regions and signal words, export their CUDA IPC handles
+ *   (hmj_dist_handle_bytes() bytes).
+ * connect: all ranks' handles in rank order (world x hmj_dist_handle_bytes() bytes).
+ * join_u64: ONE call per join on every rank (same order on all ranks), no host barrier around it:
+ *   level 1 over the rank's rows of R, then of S, cut on the GPU bits and written into the owners'
+ *   memory over NVLink; the owners' local levels of R run while S is still in flight; then the
+ *   bucket join of the rank's own hash range.  The GPUs meet through release/acquire flags in each
+ *   other's memory.  Row ids are global: r_rowid_base + i / s_rowid_base + i.  *ok = 0 when a
+ *   region overflowed here or a peer did not answer (every rank then uses the NCCL path).
+ * last_exchange: pairs this rank wrote into other ranks' memory in the last join and the pairs of
+ *   R and S it received, read back from the device cursors.
+ * teardown: every rank must have finished its last join (a barrier) before any rank tears down. */
+int hmj_dist_handle_bytes(void);
 int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_total, unsigned char* handles_out);
 int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles);
-int hmj_dist_begin(hmj_ctx* ctx);
-int hmj_dist_scatter(hmj_ctx* ctx, int side, const uint64_t* d_keys, size_t n, uint32_t rowid_base);
-int hmj_dist_join(hmj_ctx* ctx, uint64_t* h_num_pairs, int* ok);
+int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr, uint32_t r_rowid_base,
+                      const uint64_t* d_skeys, size_t ns, uint32_t s_rowid_base,
+                      uint64_t* h_num_pairs, int* ok);
+int hmj_dist_last_exchange(hmj_ctx* ctx, uint64_t* sent_pairs_remote, uint64_t* received_r,
+                           uint64_t* received_s);
 int hmj_dist_teardown(hmj_ctx* ctx);
+
+/* ---- benchmark relation generators on the device (datagen.cu; harness, not on the join path) --
+ * The reference builds its inputs on the host with create_strvec (strgen.cc:28-61: ceil(sqrt(n))
+ * base words w_i, then "w_i-w_j" row-major, shuffled); these produce the same shapes in HBM.
+ * permute: d_out[i] = P(d_in[i]) (d_in NULL: P(in_base + i)), P a seeded bijection of [0, domain).
+ * zipf: d_out_rank[i] = first k with d_cdf[k] > u(seed, row_base + i), u uniform in [0,1).
+ * strgen_lengths / strgen_write: length and bytes of strgen key d_key_ids[i] (id < q: w_id, else
+ * w_a-w_b with (a, b) = divmod(id - q, q)) over a device word table (offsets[q+1] + chars). */
+int hmj_gen_permute(hmj_ctx* ctx, const uint32_t* d_in, uint32_t in_base, size_t n, uint32_t domain,
+                    uint32_t seed, uint32_t* d_out);
+int hmj_gen_zipf(hmj_ctx* ctx, const double* d_cdf, uint32_t n_keys, uint64_t seed, uint64_t row_base,
+                 size_t n, uint32_t* d_out_rank);
+int hmj_gen_strgen_lengths(hmj_ctx* ctx, const uint64_t* d_word_offsets, uint32_t q,
+                           const uint32_t* d_key_ids, size_t n, uint64_t* d_out_len);
+int hmj_gen_strgen_write(hmj_ctx* ctx, const uint64_t* d_word_offsets, const uint8_t* d_word_chars,
+                         uint32_t q, const uint32_t* d_key_ids, size_t n, const uint64_t* d_offsets,
+                         uint8_t* d_chars);
 
 /* ---- per-stage device timings of the last whole-operator call ------------------------ */
 typedef struct hmj_timings {
@@ -234,6 +270,9 @@ typedef struct hmj_timings {
   uint32_t kernel_launches[8];
   float kernel_ms[8];
   double kernel_bytes[8]; /* algorithmic bytes of the timed launches */
+  /* plan of the last whole-operator join */
+  uint32_t bucket_join;    /* 1: radix-partition + in-shared-memory bucket join; 0: sort + merge-path join */
+  uint32_t scatter_levels; /* bucket-scatter launches of that join (both relations) */
 } hmj_timings;
 enum hmj_kernel_class {
   HMJ_K_PASS = 0,    /* onesweep_pass_kernel (stable scatter pass) */
@@ -242,7 +281,8 @@ enum hmj_kernel_class {
   HMJ_K_JOIN = 3,    /* join_tile_kernel */
   HMJ_K_HIST = 4,    /* radix_histogram_kernel */
   HMJ_K_HASH = 5,    /* hash_strings_kernel */
-  HMJ_K_BJOIN = 6    /* bucket_join_kernel (uniform-hash whole-operator path) */
+  HMJ_K_BJOIN = 6,   /* bucket_join_kernel (uniform-hash whole-operator path) */
+  HMJ_K_XSCATTER = 7 /* level 1 of the multi-GPU join: bucket scatter into the owners' memory over NVLink */
 };
 int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
 /* on != 0: bracket every onesweep-pass launch with CUDA events on the context's stream and

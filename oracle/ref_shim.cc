@@ -82,6 +82,23 @@ double join_rel(Rel& r, Rel& s, int threads, uint32_t* out_r, uint32_t* out_s, s
   return t1 - t0;
 }
 
+// The unordered_map build + probe loop that hashjoin_bench.cc:41-53 (BM_hash_join_raw) times
+// beside BM_HashMergeJoin.  That file is a google-benchmark main and cannot be built here, so its
+// two loops are restated over the same containers (reserve outside the timed part, as there).
+template <typename Rel>
+double hash_join_raw_rel(const Rel& r, const Rel& s, uint64_t* sum_out) {
+  typedef typename Rel::value_type::first_type Key;
+  std::unordered_map<Key, uint64_t> s_map;
+  s_map.reserve(s.size());
+  const double t0 = now_s();
+  uint64_t sum = 0;
+  for (const auto& s_kv : s) s_map[s_kv.first] = s_kv.second;
+  for (const auto& r_kv : r) sum += r_kv.second + s_map[r_kv.first];
+  const double t1 = now_s();
+  if (sum_out) *sum_out = sum;
+  return t1 - t0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -158,6 +175,17 @@ double ref_join_strings(const uint64_t* roff, const uint8_t* rchars, size_t nr, 
                         uint32_t* out_s, size_t cap, uint64_t* num_pairs, uint64_t* sum) {
   StrRel r = make_str_rel(roff, rchars, nr), s = make_str_rel(soff, schars, ns);
   return join_rel(r, s, threads, out_r, out_s, cap, num_pairs, sum);
+}
+
+// std::unordered_map build (S) + probe (R), hashjoin_bench.cc:41-53.  Returns seconds.
+double ref_hash_join_raw_u64(const uint64_t* rk, size_t nr, const uint64_t* sk, size_t ns, uint64_t* sum) {
+  IntRel r = make_int_rel(rk, nr), s = make_int_rel(sk, ns);
+  return hash_join_raw_rel(r, s, sum);
+}
+double ref_hash_join_raw_strings(const uint64_t* roff, const uint8_t* rchars, size_t nr,
+                                 const uint64_t* soff, const uint8_t* schars, size_t ns, uint64_t* sum) {
+  StrRel r = make_str_rel(roff, rchars, nr), s = make_str_rel(soff, schars, ns);
+  return hash_join_raw_rel(r, s, sum);
 }
 
 // partition_only (partitioned_hash.h:82-124): sizes of the produced partitions.

@@ -65,7 +65,7 @@ def main():
     same = bool(np.array_equal(out_r[o], r_r[q]) and np.array_equal(out_s[o], r_s[q]))
     print(json.dumps({"config": "C1 hashjoin_bench 1M x 1M strgen strings (mean key %.1f B)" % (chars.size / n),
                       "gpu_ms": ms, "gpu_tuples_per_s": 2 * n / ms * 1e3, "pairs": int(m),
-                      "uniform_path": tm["sort_uniform"] == 2,
+                      "uniform_path": tm["bucket_join"] == 1,
                       "stage_ms": {k: tm[k] for k in ("hash_ms", "sort_ms", "join_ms")},
                       "reference_1thread_s": t1, "reference_%dthreads_s" % cores: tp,
                       "reference_tuples_per_s_1t": 2 * n / t1, "pairs_equal_reference": same}), flush=True)
@@ -117,7 +117,7 @@ def main():
     tm = ctx.timings()
     print(json.dumps({"config": "C5 scaled: %d x %d strgen strings, build keys twice, Zipf(1.0) probe, 1 B200" % (n5, n5),
                       "gpu_ms": ms, "gpu_tuples_per_s": 2 * n5 / ms * 1e3, "pairs": int(m), "expected_pairs": 2 * n5,
-                      "uniform_path": tm["sort_uniform"] == 2, "sort_passes": tm["sort_passes"],
+                      "uniform_path": tm["bucket_join"] == 1, "sort_passes": tm["sort_passes"],
                       "stage_ms": {k: tm[k] for k in ("hash_ms", "sort_ms", "join_ms")}}), flush=True)
     ctx.close()
 

@@ -172,6 +172,10 @@ class Ref:
         L.ref_join_u64.argtypes = [_P, _SZ, _P, _SZ, _I, _P, _P, _SZ, _U64P, _U64P]
         L.ref_join_strings.restype = C.c_double
         L.ref_join_strings.argtypes = [_P, _P, _SZ, _P, _P, _SZ, _I, _P, _P, _SZ, _U64P, _U64P]
+        L.ref_hash_join_raw_u64.restype = C.c_double
+        L.ref_hash_join_raw_u64.argtypes = [_P, _SZ, _P, _SZ, _U64P]
+        L.ref_hash_join_raw_strings.restype = C.c_double
+        L.ref_hash_join_raw_strings.argtypes = [_P, _P, _SZ, _P, _P, _SZ, _U64P]
         L.ref_partition_counts_u64.argtypes = [_P, _SZ, _I, _I, _P]
         L.ref_partition_counts_strings.argtypes = [_P, _P, _SZ, _I, _I, _P]
 
@@ -225,6 +229,16 @@ class Ref:
             assert m.value <= cap
             return out_r[: m.value], out_s[: m.value], sm.value, t
         return m.value, None, sm.value, t
+
+    def hash_join_raw(self, rkeys, skeys):
+        """unordered_map build over S + probe with R (hashjoin_bench.cc:41-53) -> (sum, seconds)"""
+        sm = C.c_uint64()
+        if rkeys.kind == 0:
+            t = self.lib.ref_hash_join_raw_u64(_p(rkeys.u64), rkeys.n, _p(skeys.u64), skeys.n, C.byref(sm))
+        else:
+            t = self.lib.ref_hash_join_raw_strings(_p(rkeys.offsets), _p(rkeys.chars), rkeys.n,
+                                                   _p(skeys.offsets), _p(skeys.chars), skeys.n, C.byref(sm))
+        return sm.value, t
 
     def partition_counts(self, keys, threads, bits):
         out = np.zeros(1 << bits, np.uint64)
