@@ -78,6 +78,7 @@ SIGNATURES = {
     "hmj_join_strings": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
     "hmj_join_strings_range": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _I, _U64P]),
     "hmj_gather_strings": (_I, [_P, _P, _P, _P, _SZ, _P, _P]),
+    "hmj_set_join_order": (_I, [_P, _I]),
     "hmj_join_result": (_I, [_P, C.POINTER(_P), C.POINTER(_P), _U64P]),
     "hmj_join_result_copy": (_I, [_P, _P, _P, _SZ]),
     "hmj_join_result_to_host": (_I, [_P, _P, _P, _SZ]),

@@ -172,6 +172,10 @@ class Context:
                                          C.byref(m)))
         return m.value
 
+    def set_join_order(self, hash_order):
+        """True: pairs in ascending hash order, reproducible (sort + merge-path plan)"""
+        self._ck(self.lib.hmj_set_join_order(self.h, 1 if hash_order else 0))
+
     def join_result(self):
         """device views (int32 tensors) of the last whole-operator result"""
         pr, ps, m = C.c_void_p(), C.c_void_p(), C.c_uint64()

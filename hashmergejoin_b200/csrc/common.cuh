@@ -70,6 +70,12 @@ struct hmj_ctx {
   std::vector<int> prof_kind;            // kernel class of pair i (hmj_kernel_class)
   std::vector<double> prof_bytes;        // algorithmic bytes of launch i
   size_t prof_used = 0;
+  // hmj_set_join_order: pairs wanted in ascending hash order (the reference's iteration order,
+  // hashjoin.h:126-153): joins then take the sort + merge-path plan
+  bool hash_order = false;
+  // copy streams and events of the host-buffer entry points (host_api.cu), created on first use
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  std::vector<cudaEvent_t> copy_events;
   // multi-GPU join state (dist_join.cu)
   struct hmj_dist_state* dist = nullptr;
   // last whole-operator result
@@ -218,6 +224,11 @@ int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const u
                          int skip_bits, const uint64_t* roff,
                          const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
                          cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok);
+int hmj_bucket_join_launch(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
+                           const hmj_uniform_buckets& S, uint32_t cap_seg, int dshift, size_t nr,
+                           size_t ns, const uint64_t* roff, const uint8_t* rchars,
+                           const uint64_t* soff, const uint8_t* schars, uint32_t* out_r,
+                           uint32_t* out_s, size_t cap, uint64_t* d_total);
 int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
                         const hmj_uniform_buckets& S, uint32_t cap_seg, int dshift, size_t nr,
                         size_t ns, const uint64_t* roff, const uint8_t* rchars,

@@ -83,6 +83,9 @@ extern "C" int hmj_destroy(hmj_ctx* ctx) {
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
+  for (auto& ev : ctx->copy_events) cudaEventDestroy(ev);
+  if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
+  if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;

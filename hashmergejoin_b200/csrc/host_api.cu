@@ -47,6 +47,123 @@ int copy_out(hmj_ctx* ctx, T* h_dst, const T* d_src, size_t count) {
 }
 }  // namespace
 
+namespace {
+
+int ensure_copy_streams(hmj_ctx* ctx, size_t events) {
+  if (!ctx->copy_in) HMJ_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
+  if (!ctx->copy_out) HMJ_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
+  while (ctx->copy_events.size() < events) {
+    cudaEvent_t e;
+    HMJ_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ctx->copy_events.push_back(e);
+  }
+  return HMJ_OK;
+}
+
+int host_chunks_from_env() {
+  static const int v = [] {
+    const char* e = getenv("HMJ_HOST_CHUNKS");
+    const int c = e ? atoi(e) : 8;
+    return c < 1 ? 1 : c > 32 ? 32 : c;
+  }();
+  return v;
+}
+
+// One host-buffer join with the three legs overlapped.  A join's pairs depend on all of S but
+// only on the rows of R seen so far, so: S is copied in and cut into its buckets; R follows in
+// chunks, and as soon as a chunk has landed it is cut into the same buckets and joined against
+// S's, its pairs appended to the result and copied out while the next chunk is still arriving
+// (the host link is full duplex).  The call then costs about the input copy plus one chunk's
+// tail instead of copy + join + copy.  The union of the chunks' pairs is the join (every R row
+// is in exactly one chunk).  *done = 0: the plan does not apply (small or skewed input, result
+// larger than expected) and nothing has been delivered -- the caller runs the plain path, the
+// inputs are complete in d_r / d_s by then.
+int join_u64_host_chunked(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, const uint64_t* h_skeys,
+                          size_t ns, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap,
+                          uint64_t* h_num_pairs, uint64_t* d_r, uint64_t* d_s, int* done) {
+  *done = 0;
+  const int chunks = host_chunks_from_env();
+  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, 0);
+  const char* e = getenv("HMJ_JOIN_UNIFORM");
+  const bool eligible = chunks > 1 && p.levels != 0 && nr >= ((size_t)chunks << 16) && ns > 0 &&
+                        !(e && atoi(e) == 0) && !ctx->hash_order;
+  HMJ_TRY(ensure_copy_streams(ctx, (size_t)chunks + 2));
+  cudaStream_t st = ctx->stream, cin = ctx->copy_in, cout = ctx->copy_out;
+  // chunk boundaries on multiples of 4096 rows: tiles of the scatter stay 16-byte aligned
+  const size_t per = eligible ? ((nr / chunks + 4095) & ~size_t(4095)) : nr;
+  // the copy stream must not overtake work still queued on the compute stream that reads the
+  // staging buffers of an earlier call
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->copy_events[chunks + 1], st));
+  HMJ_CUDA(ctx, cudaStreamWaitEvent(cin, ctx->copy_events[chunks + 1], 0));
+  if (ns) HMJ_CUDA(ctx, cudaMemcpyAsync(d_s, h_skeys, ns * 8, cudaMemcpyHostToDevice, cin));
+  HMJ_CUDA(ctx, cudaEventRecord(ctx->copy_events[chunks], cin));
+  int n_chunks = 0;
+  for (size_t off = 0; off < nr; off += per, ++n_chunks) {
+    const size_t n = nr - off < per ? nr - off : per;
+    HMJ_CUDA(ctx, cudaMemcpyAsync(d_r + off, h_rkeys + off, n * 8, cudaMemcpyHostToDevice, cin));
+    HMJ_CUDA(ctx, cudaEventRecord(ctx->copy_events[n_chunks], cin));
+  }
+  if (!eligible) {
+    HMJ_CUDA(ctx, cudaStreamSynchronize(cin));
+    return HMJ_OK;
+  }
+  ctx->tm.sort_passes = ctx->tm.sort_finishes = ctx->tm.sort_fallbacks = ctx->tm.sort_uniform = 0;
+  ctx->tm.bucket_join = 0;
+  ctx->tm.scatter_levels = 0;
+  // result buffers and the pair counter
+  size_t dcap = ctx->ws[WS_OUT_R].bytes / 4;
+  const size_t guess = nr > ns ? nr : ns;
+  if (dcap < guess) dcap = guess;
+  uint32_t *out_r = nullptr, *out_s = nullptr;
+  uint64_t* d_total = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_R, dcap, &out_r));
+  HMJ_TRY(hmj_ws(ctx, WS_OUT_S, dcap, &out_s));
+  HMJ_TRY(hmj_ws(ctx, WS_JOIN_TILES, 4, &d_total));
+  dcap = ctx->ws[WS_OUT_R].bytes / 4;
+  if (ctx->ws[WS_OUT_S].bytes / 4 < dcap) dcap = ctx->ws[WS_OUT_S].bytes / 4;
+  HMJ_TRY(hmj_fill_async(ctx, d_total, 0, 32, st));
+  // S into its buckets
+  hmj_uniform_buckets Sb, Rb;
+  HMJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->copy_events[chunks], 0));
+  HMJ_TRY(hmj_uniform_scatter(ctx, d_s, nullptr, ns, 0, p, 1, &Sb));
+  uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
+  uint64_t m_prev = 0;
+  bool failed = false;
+  int c = 0;
+  for (size_t off = 0; off < nr && !failed; off += per, ++c) {
+    const size_t n = nr - off < per ? nr - off : per;
+    HMJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->copy_events[c], 0));
+    HMJ_TRY(hmj_uniform_scatter(ctx, d_r + off, nullptr, n, (uint32_t)off, p, 0, &Rb));
+    HMJ_TRY(hmj_bucket_join_launch(ctx, HMJ_KEY_U64, Rb, Sb, p.cap_seg, 64 - p.skip - p.qb - 12, n, ns,
+                                   nullptr, nullptr, nullptr, nullptr, out_r, out_s, dcap, d_total));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_total, 8, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h + 1), Rb.flag, 4, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h + 1) + 1, Sb.flag, 4, cudaMemcpyDeviceToHost, st));
+    HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+    const uint64_t m = h[0];
+    if (h[1] != 0 || m > dcap || ((h_out_r || h_out_s) && m > cap)) {
+      failed = true;  // skewed hashes, or more pairs than the buffers hold: the plain path decides
+      break;
+    }
+    if (m > m_prev) {
+      // the chunk's pairs leave while the next chunk arrives (the kernels that wrote them are done)
+      if (h_out_r) HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_r + m_prev, out_r + m_prev, (m - m_prev) * 4, cudaMemcpyDeviceToHost, cout));
+      if (h_out_s) HMJ_CUDA(ctx, cudaMemcpyAsync(h_out_s + m_prev, out_s + m_prev, (m - m_prev) * 4, cudaMemcpyDeviceToHost, cout));
+    }
+    m_prev = m;
+  }
+  HMJ_CUDA(ctx, cudaStreamSynchronize(cin));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(cout));
+  if (failed) return HMJ_OK;
+  ctx->tm.bucket_join = 1;
+  ctx->last_pairs = m_prev;
+  *h_num_pairs = m_prev;
+  *done = 1;
+  return HMJ_OK;
+}
+
+}  // namespace
+
 extern "C" int hmj_join_u64_host(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr,
                                  const uint64_t* h_skeys, size_t ns, uint32_t* h_out_r,
                                  uint32_t* h_out_s, size_t cap, uint64_t* h_num_pairs) {
@@ -55,12 +172,22 @@ extern "C" int hmj_join_u64_host(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t n
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
   uint64_t *dr = nullptr, *ds = nullptr;
   mark(ctx, "enter");
+  HMJ_TRY(hmj_ws(ctx, WS_IN_0, nr, &dr));
+  HMJ_TRY(hmj_ws(ctx, WS_IN_1, ns, &ds));
   {
+    // one call at a time per GPU owns the host link's input direction (see CopyTurn)
     CopyTurn turn(ctx, TURN_H2D);
     mark(ctx, "h2d turn");
-    HMJ_TRY(stage_in(ctx, WS_IN_0, h_rkeys, nr, &dr));
-    HMJ_TRY(stage_in(ctx, WS_IN_1, h_skeys, ns, &ds));
-    HMJ_TRY(turn.finish());
+    int done = 0;
+    const int rc = join_u64_host_chunked(ctx, h_rkeys, nr, h_skeys, ns, h_out_r, h_out_s, cap,
+                                         h_num_pairs, dr, ds, &done);
+    const int rc2 = turn.finish();
+    HMJ_TRY(rc);
+    HMJ_TRY(rc2);
+    if (done) {
+      mark(ctx, "leave (chunked)");
+      return HMJ_OK;
+    }
   }
   mark(ctx, "h2d done");
   HMJ_TRY(hmj_join_u64(ctx, dr, nr, ds, ns, h_num_pairs));

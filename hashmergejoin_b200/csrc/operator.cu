@@ -189,6 +189,12 @@ extern "C" int hmj_join_result_copy(hmj_ctx* ctx, uint32_t* d_out_r, uint32_t* d
   return HMJ_OK;
 }
 
+extern "C" int hmj_set_join_order(hmj_ctx* ctx, int hash_order) {
+  if (!ctx) return HMJ_EARG;
+  ctx->hash_order = hash_order != 0;
+  return HMJ_OK;
+}
+
 extern "C" int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out) {
   if (!ctx || !out) return HMJ_EARG;
   HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

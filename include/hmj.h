@@ -155,6 +155,12 @@ int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, const uint8
 int hmj_gather_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const uint8_t* d_chars,
                        const uint32_t* d_rows, size_t n, const uint64_t* d_out_offsets,
                        uint8_t* d_out_chars);
+/* Order of the result pairs of the whole-operator joins on this context.  0 (default): whatever
+ * the faster plan yields (bucket arrival order on the bucket path, not reproducible between
+ * runs).  1: ascending hash order, equal hashes by (build row, probe row) position in the sorted
+ * relations -- the order HashMergeJoin::iterator walks in (hashjoin.h:126-153), identical between
+ * runs; the join then always takes the sort + merge-path plan. */
+int hmj_set_join_order(hmj_ctx* ctx, int hash_order);
 /* device pointers to the last join's pairs (valid until the next join / destroy). */
 int hmj_join_result(hmj_ctx* ctx, const uint32_t** d_out_r, const uint32_t** d_out_s,
                     uint64_t* num_pairs);

@@ -38,8 +38,9 @@ def expected_pairs(rk, sk):
 
 
 def canon(a, b):
-    o = np.lexsort((b, a))
-    return a[o], b[o]
+    """the pair list in canonical order, as one sorted array of (build_row << 32 | probe_row)"""
+    w = np.sort((a.astype(np.uint64) << np.uint64(32)) | b.astype(np.uint64))
+    return w, w
 
 
 def _rank_main(rank, world, port, rows_total, q):
@@ -169,16 +170,17 @@ def test_dist_join_2_gpus_one_local_level():
 
 
 def test_dist_join_2_gpus_two_local_levels():
-    # 64M rows over 2 GPUs: level 1 on the GPU bit, two local levels below (C4's plan shape)
+    # 16M rows over 2 GPUs: level 1 on the GPU bit, two local levels below (C4's plan shape)
     _need(2)
-    run_world(2, 1 << 25)
+    run_world(2, 1 << 24)
 
 
 def test_dist_join_4_gpus():
     _need(4)
-    run_world(4, 1 << 25)
+    run_world(4, 1 << 24)
 
 
 def test_dist_join_8_gpus():
+    # 32M rows over 8 GPUs: 3 GPU bits, then 5 + 5 bits locally
     _need(8)
-    run_world(8, 1 << 26)
+    run_world(8, 1 << 25)
