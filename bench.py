@@ -21,7 +21,9 @@ Workloads (BASELINE.json configs):
   c5   strgen strings, build keys twice, Zipf(1.0) probe; --rows sets rows per side (default
        64M on one GPU; 512M x 512M = configs[4] with --gpus 8)
   c3-dense      c3 with keys 0..N-1 (identity hash: every row in one bucket of the top bits)
-  c3-sortmerge  c3 forced through the sort + merge-path plan (HMJ_JOIN_UNIFORM=0)
+  c3-sortmerge  c3 with both relations sorted and merge-joined (HMJ_JOIN_UNIFORM=0)
+  c3-onesweep   ... and the sort done by stable LSD passes (HMJ_SORT_UNIFORM=0): the literal
+                hash -> onesweep radix sort -> merge-path join pipeline
   small, mid    4M / 64M u64 rows per side (smoke / profiling sizes)
 metric  = joined input tuples/sec = (|R|+|S|) / step time  (c2: keys/sec, stated in the line).
 value   = inputs already resident in HBM (CUDA events).
@@ -58,7 +60,8 @@ WORKLOADS = {
     "c4": ("u64", 2 ** 30, "hash-merge join 1B x 1B int keys radix-partitioned across N B200 (level-1 scatter over NVLink)"),
     "c5": ("zipf", 64 * M, "skewed many-to-many join, strgen strings, build keys twice, Zipf(1.0) probe, full-key collision check"),
     "c3-dense": ("u64", 256 * M, "hash-merge join 256M x 256M dense int keys 0..N-1 (identity hash: skewed top bits)"),
-    "c3-sortmerge": ("u64", 256 * M, "hash-merge join 256M x 256M 64-bit int keys through the onesweep sort + merge-path plan"),
+    "c3-sortmerge": ("u64", 256 * M, "hash-merge join 256M x 256M 64-bit int keys: both relations sorted (scatter levels + in-smem finish), then the merge-path join"),
+    "c3-onesweep": ("u64", 256 * M, "hash-merge join 256M x 256M 64-bit int keys: onesweep-style stable LSD passes, then the merge-path join (the north-star's literal pipeline)"),
     "small": ("u64", 4 * M, "hash-merge join 4M x 4M 64-bit int keys (smoke-sized)"),
     "mid": ("u64", 64 * M, "hash-merge join 64M x 64M 64-bit int keys (profiling-sized)"),
 }
@@ -69,6 +72,13 @@ KERNEL_NAMES = ["onesweep_pass_kernel", "bucket_scatter_tma_kernel", "segment_so
                 "bucket_scatter_tma_kernel<DIST> (level 1 over NVLink)"]
 PATH_BUCKET = "radix-partition + in-smem bucket join"
 PATH_SORT = "onesweep sort + merge-path join"
+PATH_SCATTER_SORT = "bucket-scatter sort + merge-path join"
+
+
+def path_name(tm):
+    if tm["bucket_join"]:
+        return PATH_BUCKET
+    return PATH_SORT if tm["sort_passes"] else PATH_SCATTER_SORT
 
 
 def log(*a):
@@ -408,8 +418,10 @@ def run_gpu_u64(args, wl):
     rows_total = args.rows or rows_total
     assert rows_total & (rows_total - 1) == 0, "u64 workloads need a power-of-two row count (row permutation)"
     dense = wl == "c3-dense"
-    if wl == "c3-sortmerge":
+    if wl in ("c3-sortmerge", "c3-onesweep"):
         os.environ["HMJ_JOIN_UNIFORM"] = "0"
+    if wl == "c3-onesweep":
+        os.environ["HMJ_SORT_UNIFORM"] = "0"
     rows = rows_total // world  # rows per side owned by this rank
     # same key set on both sides, two different row orders (hashjoin_bench.cc:112-113): 1:1
     lo = rank * rows
@@ -491,7 +503,7 @@ def run_gpu_u64(args, wl):
                        "key": "u64 dense 0..N-1 in a permuted row order" if dense else
                               "u64 (splitmix64 of a row permutation; same key set both sides)",
                        "l2": "inputs (2 x %.1f GB) and every intermediate exceed the 126 MB L2; no flush needed" % (rows * 8 / 1e9),
-                       "path": PATH_BUCKET if tm["bucket_join"] else PATH_SORT,
+                       "path": path_name(tm),
                        "bucket_join": bool(tm["bucket_join"]), "scatter_levels_per_join": tm["scatter_levels"],
                        "sort_passes_per_join": tm["sort_passes"], "bucket_finishes_per_join": tm["sort_finishes"],
                        "sort_fallbacks": tm["sort_fallbacks"],
@@ -741,7 +753,9 @@ def run_gpu_strings(args, wl):
         hn = [x.numpy().view(np.uint64) if x.dtype == torch.int64 else x.numpy() for x in hb]
         e2e_steps = max(1, min(args.steps, 3))
         if kind == "sort":
-            call = lambda: ctx.hash_sort_strings_host(hn[0], hn[1])
+            p_h = torch.empty(rows, dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+            p_v = torch.empty(rows, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
+            call = lambda: ctx.hash_sort_strings_host(hn[0], hn[1], p_h, p_v)
             d2h = rows * 12
         else:
             o_r = torch.empty(expect_pairs, dtype=torch.int32).pin_memory().numpy().view(np.uint32)
@@ -784,7 +798,7 @@ def run_gpu_strings(args, wl):
                              "inputs (%.0f MB) FIT the 126 MB L2 and are re-read from it between steps: the step is launch-latency bound, not HBM bound" % (key_bytes / 1e6 + rows * 16e-6),
                        "path": "hash + bucket scatter + segment sort" if kind == "sort" and tm["sort_uniform"] else
                                "hash + onesweep passes" if kind == "sort" else
-                               (PATH_BUCKET if tm["bucket_join"] else PATH_SORT),
+                               path_name(tm),
                        "bucket_join": bool(tm["bucket_join"]), "scatter_levels_per_join": tm["scatter_levels"],
                        "sort_passes_per_join": tm["sort_passes"], "sort_fallbacks": tm["sort_fallbacks"],
                        "parallelism": "hash-range partition x%d%s" % (world, " (NCCL all-to-all of rows + key bytes)" if world > 1 else "")},

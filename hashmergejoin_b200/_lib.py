@@ -84,6 +84,8 @@ SIGNATURES = {
     "hmj_join_result_to_host": (_I, [_P, _P, _P, _SZ]),
     "hmj_join_u64_host": (_I, [_P, _P, _SZ, _P, _SZ, _P, _P, _SZ, _U64P]),
     "hmj_join_strings_host": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
+    "hmj_host_alloc": (_I, [C.POINTER(_P), _SZ]),
+    "hmj_host_free": (_I, [_P]),
     "hmj_hash_sort_u64_host": (_I, [_P, _P, _SZ, _P, _P]),
     "hmj_hash_sort_strings_host": (_I, [_P, _P, _P, _SZ, _P, _P]),
     "hmj_sort_pairs_host": (_I, [_P, _P, _P, _SZ, _P, _P]),

@@ -263,15 +263,18 @@ class Context:
                                                 _hptr(out_r), _hptr(out_s), cap, C.byref(m)))
         return m.value
 
-    def hash_sort_u64_host(self, keys):
+    def hash_sort_u64_host(self, keys, out_hash=None, out_rowid=None):
         n = keys.size
-        h, r = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        h = out_hash if out_hash is not None else np.empty(n, np.uint64)
+        r = out_rowid if out_rowid is not None else np.empty(n, np.uint32)
         self._ck(self.lib.hmj_hash_sort_u64_host(self.h, _hptr(keys), n, _hptr(h), _hptr(r)))
         return h, r
 
-    def hash_sort_strings_host(self, offsets, chars):
+    def hash_sort_strings_host(self, offsets, chars, out_hash=None, out_rowid=None):
+        """out_hash / out_rowid: caller's (pinned) result arrays; fresh pageable ones otherwise"""
         n = offsets.size - 1
-        h, r = np.empty(n, np.uint64), np.empty(n, np.uint32)
+        h = out_hash if out_hash is not None else np.empty(n, np.uint64)
+        r = out_rowid if out_rowid is not None else np.empty(n, np.uint32)
         self._ck(self.lib.hmj_hash_sort_strings_host(self.h, _hptr(offsets), _hptr(chars), n,
                                                      _hptr(h), _hptr(r)))
         return h, r

@@ -649,28 +649,109 @@ int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
   return hmj_fail(ctx, HMJ_ECAPACITY, "bucket join: result did not fit twice", __FILE__, __LINE__);
 }
 
+namespace {
+constexpr uint32_t SAMPLE_PER_SIDE = 32768;
+
+__global__ void __launch_bounds__(256)
+sample_keys_kernel(const uint64_t* __restrict__ r, size_t nr, const uint64_t* __restrict__ s, size_t ns,
+                   uint64_t* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < SAMPLE_PER_SIDE) {
+    out[i] = r[(size_t)((unsigned __int128)i * nr / SAMPLE_PER_SIDE)];
+  } else if (i < 2 * SAMPLE_PER_SIDE) {
+    out[i] = s[(size_t)((unsigned __int128)(i - SAMPLE_PER_SIDE) * ns / SAMPLE_PER_SIDE)];
+  }
+}
+}  // namespace
+
+// Looks at 32768 evenly spaced hashes of each relation before anything is moved:
+//  * top bits that every sampled hash of BOTH relations shares (identity-hashed dense integer keys
+//    0..N-1 share their upper 64 - log2(N) bits) are skipped by the bucket plan, so such keys cut
+//    as evenly as random ones; level 1 verifies the assumption on every row;
+//  * a level-1 region that holds more than 1.5x its share of the sample (Zipf heads, heavy
+//    duplicates) means the padded buckets would overflow: *skewed = 1 and the caller goes to the
+//    sort + merge-path plan without paying for a failed scatter attempt.
+// Costs one small kernel, a 512 KB copy and a stream synchronisation (~0.1 ms), so only joins of
+// at least 2^22 rows are sampled.
+int hmj_sample_plan(hmj_ctx* ctx, const uint64_t* r_hash, size_t nr, const uint64_t* s_hash,
+                    size_t ns, hmj_uniform_plan* p, int* skewed) {
+  *skewed = 0;
+  cudaStream_t st = ctx->stream;
+  uint64_t* d_sample = nullptr;
+  HMJ_TRY(hmj_ws(ctx, WS_JOIN_MISC, 2 * SAMPLE_PER_SIDE, &d_sample));
+  if (ctx->sample_host.size() < 2 * SAMPLE_PER_SIDE) {
+    // (pinned once per context; the join never allocates in steady state)
+    ctx->sample_host.resize(2 * SAMPLE_PER_SIDE);
+    cudaHostRegister(ctx->sample_host.data(), ctx->sample_host.size() * 8, cudaHostRegisterDefault);
+    cudaGetLastError();
+  }
+  sample_keys_kernel<<<2 * SAMPLE_PER_SIDE / 256, 256, 0, st>>>(r_hash, nr, s_hash, ns, d_sample);
+  HMJ_LAUNCHED(ctx);
+  uint64_t* h = ctx->sample_host.data();
+  HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_sample, 2 * SAMPLE_PER_SIDE * 8, cudaMemcpyDeviceToHost, st));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(st));
+  uint64_t diff = 0;
+  for (uint32_t i = 0; i < 2 * SAMPLE_PER_SIDE; ++i) diff |= h[i] ^ h[0];
+  int skip = diff ? __builtin_clzll(diff) : 64;
+  const size_t n_plan = nr > ns ? nr : ns;
+  hmj_uniform_plan q = hmj_uniform_plan_for(n_plan, 0);
+  if (q.levels == 0) return HMJ_OK;
+  if (skip > 64 - q.qb - 12) skip = 64 - q.qb - 12;
+  if (skip > 0) {
+    q = hmj_uniform_plan_for(n_plan, skip);
+    q.check_prefix = true;
+    q.prefix = h[0] >> (64 - skip);
+  }
+  // share of the sample per level-1 region
+  uint32_t hist[2][512] = {};
+  const int shift = 64 - q.skip - q.bits[0];
+  const uint32_t mask = (1u << q.bits[0]) - 1;
+  for (uint32_t i = 0; i < 2 * SAMPLE_PER_SIDE; ++i) hist[i / SAMPLE_PER_SIDE][(uint32_t)(h[i] >> shift) & mask]++;
+  const uint32_t expect = SAMPLE_PER_SIDE >> q.bits[0];
+  for (int side = 0; side < 2; ++side) {
+    ctx->sample_skewed[side] = false;
+    for (uint32_t b = 0; b <= mask; ++b)
+      if (hist[side][b] > expect + expect / 2 + 64) ctx->sample_skewed[side] = true;
+    if (ctx->sample_skewed[side]) *skewed = 1;
+  }
+  *p = q;
+  return HMJ_OK;
+}
+
 // Whole-operator join through the uniform path: scatter R and S into the same 2^qb buckets, join
 // bucket by bucket.  *ok = 0 when the inputs are not eligible or a bucket overflowed (the host
 // then sorts both relations and merge-joins them); on success the pairs are in the context's
 // result buffers (WS_OUT_R / WS_OUT_S) and *h_num_pairs is their number.
 // kind = HMJ_KEY_U64: r_hash / s_hash are the key columns themselves.  HMJ_KEY_STRING: they are
 // the hash columns and the offsets/chars arrays give the keys for verification.
+// skip_bits > 0: the caller knows that all hashes share that many top bits (a rank's hash range).
 int hmj_join_uniform_try(hmj_ctx* ctx, int kind, const uint64_t* r_hash, const uint32_t* r_rowid,
                          size_t nr, const uint64_t* s_hash, const uint32_t* s_rowid, size_t ns,
                          int skip_bits, const uint64_t* roff,
                          const uint8_t* rchars, const uint64_t* soff, const uint8_t* schars,
                          cudaEvent_t ev_partitioned, uint64_t* h_num_pairs, int* ok) {
   *ok = 0;
+  ctx->sample_skewed[0] = ctx->sample_skewed[1] = false;
   if (nr == 0 || ns == 0) return HMJ_OK;
-  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, skip_bits);
+  hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, skip_bits);
   if (p.levels == 0) return HMJ_OK;
+  const char* e = getenv("HMJ_JOIN_UNIFORM");
+  if (e && atoi(e) == 0) return HMJ_OK;
+  if (ctx->hash_order) return HMJ_OK;  // the caller wants hash order: sort + merge-path plan
+  static const bool sampling = [] {
+    const char* s = getenv("HMJ_JOIN_SAMPLE");
+    return !(s && atoi(s) == 0);
+  }();
+  if (sampling && skip_bits == 0 && nr + ns >= ((size_t)1 << 22) && nr >= SAMPLE_PER_SIDE && ns >= SAMPLE_PER_SIDE &&
+      ((reinterpret_cast<uintptr_t>(r_hash) | reinterpret_cast<uintptr_t>(s_hash)) & 15) == 0) {
+    int skewed = 0;
+    HMJ_TRY(hmj_sample_plan(ctx, r_hash, nr, s_hash, ns, &p, &skewed));
+    if (skewed || p.levels == 0) return HMJ_OK;
+  }
   if ((p.bits[0] > 8 || p.bits[1] > 8) &&
       ((reinterpret_cast<uintptr_t>(r_hash) | reinterpret_cast<uintptr_t>(s_hash) |
         reinterpret_cast<uintptr_t>(r_rowid) | reinterpret_cast<uintptr_t>(s_rowid)) & 15) != 0)
     return HMJ_OK;
-  const char* e = getenv("HMJ_JOIN_UNIFORM");
-  if (e && atoi(e) == 0) return HMJ_OK;
-  if (ctx->hash_order) return HMJ_OK;  // the caller wants hash order: sort + merge-path plan
   hmj_uniform_buckets R, S;
   HMJ_TRY(hmj_uniform_scatter(ctx, r_hash, r_rowid, nr, 0, p, 0, &R));
   HMJ_TRY(hmj_uniform_scatter(ctx, s_hash, s_rowid, ns, 0, p, 1, &S));

@@ -221,7 +221,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
                           uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag,
                           uint32_t* __restrict__ tile_counter, const hmj_peer_regions peers,
-                          int region_shift) {
+                          int region_shift, uint64_t prefix, int prefix_bits) {
   using Cfg = UtCfg<UT_THREADS, RANK>;
   constexpr int UT_TILE = Cfg::TILE;
   constexpr size_t UT_BUF_BYTES = Cfg::BUF_BYTES;
@@ -338,6 +338,9 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 
     uint64_t key[UT_ITEMS];
     uint16_t slot[UT_ITEMS];
+    // prefix_bits > 0 (first level of a plan that skips the hash bits all rows were found to share
+    // in a sample): a row with other top bits would land in a wrong bucket -- it voids the attempt
+    bool stray = false;
     if (RANK == 0) {
 #pragma unroll
       for (int k = 0; k < UT_ITEMS; ++k) {
@@ -345,6 +348,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
         if (i < valid) {
           key[k] = b_keys[i];
           slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+          if (prefix_bits) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
         }
       }
     } else {
@@ -357,6 +361,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
         key[k] = live ? b_keys[i] : 0;
         // rows past the end of a partial tile share the digit 256, which no counter holds
         const uint32_t dig = live ? (uint32_t)(key[k] >> shift) & mask : 256u;
+        if (prefix_bits && live) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
         uint32_t peers_of;
         if (RANK == 1) {
           peers_of = __match_any_sync(0xffffffffu, dig);
@@ -439,9 +444,9 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
         b_vals[p] = val[k];
       }
     }
-    bool over = false;
+    bool over = stray;
     if (tid < bins) {
-      over = c != 0 && (old > out_cap || c > out_cap - old);
+      over |= c != 0 && (old > out_cap || c > out_cap - old);
       s_gbase[tid] = bucket * out_cap + old - s_off[tid];
     }
     if (__syncthreads_or(over)) {
@@ -540,6 +545,8 @@ struct ScatterLaunch {
   uint32_t *cursors, *flag, *tile_counter;  // tile_counter: zeroed by the caller
   const hmj_peer_regions* peers;            // != nullptr: regions on the GPUs of the job (level 1)
   int region_shift;
+  uint64_t prefix;                          // prefix_bits > 0: every key's top bits must equal prefix
+  int prefix_bits;
 };
 
 template <int T, int B, bool DIST, int RANK>
@@ -554,7 +561,7 @@ int launch_tma(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaS
                                    a.tiles_per_region, a.total_tiles, a.iota_base, a.keys_out,
                                    a.vals_out, a.shift, a.bits, a.out_cap, a.cursors, a.flag,
                                    a.tile_counter, a.peers ? *a.peers : hmj_peer_regions(),
-                                   a.region_shift);
+                                   a.region_shift, a.prefix, a.prefix_bits);
   HMJ_LAUNCHED(ctx);
   ctx->tm.scatter_levels++;
   return HMJ_OK;
@@ -604,6 +611,15 @@ hmj_uniform_plan hmj_uniform_plan_for(size_t n_plan, int skip_bits) {
     p.levels = 2;
     p.bits[0] = (qb + 1) / 2;
     p.bits[1] = qb - p.bits[0];
+    // HMJ_UNIFORM_BITS0: width of the first level (scripts/sweep_bits.py, the counterpart of the
+    // reference's find_k_bench.cc:116-129 sweep of the partition width)
+    if (const char* e = getenv("HMJ_UNIFORM_BITS0")) {
+      const int v = atoi(e);
+      if (v >= 1 && v <= 9 && qb - v >= 1 && qb - v <= 9) {
+        p.bits[0] = v;
+        p.bits[1] = qb - v;
+      }
+    }
   }
   return p;
 }
@@ -663,8 +679,10 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
       a.keys_out = k_out1; a.vals_out = v_out1;
       a.shift = 64 - p.skip - p.bits[0]; a.bits = p.bits[0]; a.out_cap = cap_out1;
       a.cursors = d_cur1; a.flag = d_flag; a.tile_counter = d_words + 1;
+      a.prefix = p.prefix; a.prefix_bits = p.check_prefix ? p.skip : 0;
       HMJ_TRY(launch_scatter(ctx, a, 0, st));
     } else {
+      HMJ_ARG(ctx, !p.check_prefix);
       HMJ_CUDA(ctx, cudaFuncSetAttribute(bucket_scatter_kernel,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)US_SMEM));
       const uint32_t tiles = (uint32_t)hmj_div_up(n, US_TILE);

@@ -73,6 +73,10 @@ struct hmj_ctx {
   // hmj_set_join_order: pairs wanted in ascending hash order (the reference's iteration order,
   // hashjoin.h:126-153): joins then take the sort + merge-path plan
   bool hash_order = false;
+  // set by a join whose sample found a relation skewed, consumed by the next sort of pairs
+  bool next_sort_skewed = false;
+  bool sample_skewed[2] = {false, false};  // (R, S) verdict of the last hmj_sample_plan
+  std::vector<uint64_t> sample_host;  // page-locked landing area of hmj_sample_plan
   // copy streams and events of the host-buffer entry points (host_api.cu), created on first use
   cudaStream_t copy_in = nullptr, copy_out = nullptr;
   std::vector<cudaEvent_t> copy_events;
@@ -205,6 +209,10 @@ struct hmj_uniform_plan {
   int qb;            // total prefix bits = bits[0] + bits[1]
   int skip;          // topmost hash bits shared by all rows (multi-GPU hash range), not used
   uint32_t cap_seg;  // slots per final bucket
+  // skip found by sampling (dense integer keys): level 1 checks every key's top `skip` bits
+  // against `prefix` and voids the attempt when one differs
+  bool check_prefix;
+  uint64_t prefix;
 };
 struct hmj_uniform_buckets {
   uint64_t* keys;     // bucket b at [b * cap_seg ...)
@@ -234,6 +242,8 @@ int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
                         size_t ns, const uint64_t* roff, const uint8_t* rchars,
                         const uint64_t* soff, const uint8_t* schars, uint64_t* h_num_pairs,
                         int* ok);
+int hmj_sample_plan(hmj_ctx* ctx, const uint64_t* r_hash, size_t nr, const uint64_t* s_hash,
+                    size_t ns, hmj_uniform_plan* p, int* skewed);
 int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                          uint64_t* keys_out, uint32_t* vals_out, int* ok);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,

@@ -84,6 +84,7 @@ extern "C" int hmj_destroy(hmj_ctx* ctx) {
     if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->prof_events) cudaEventDestroy(ev);
   for (auto& ev : ctx->copy_events) cudaEventDestroy(ev);
+  if (!ctx->sample_host.empty()) cudaHostUnregister(ctx->sample_host.data());
   if (ctx->copy_in) cudaStreamDestroy(ctx->copy_in);
   if (ctx->copy_out) cudaStreamDestroy(ctx->copy_out);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);

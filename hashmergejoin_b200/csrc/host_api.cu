@@ -201,6 +201,25 @@ extern "C" int hmj_join_u64_host(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t n
   return HMJ_OK;
 }
 
+extern "C" int hmj_host_alloc(void** out, size_t bytes) {
+  if (!out) return HMJ_EARG;
+  *out = nullptr;
+  const cudaError_t e = cudaMallocHost(out, bytes ? bytes : 1);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return e == cudaErrorMemoryAllocation ? HMJ_ENOMEM : HMJ_ECUDA;
+  }
+  return HMJ_OK;
+}
+
+extern "C" int hmj_host_free(void* p) {
+  if (p && cudaFreeHost(p) != cudaSuccess) {
+    cudaGetLastError();
+    return HMJ_ECUDA;
+  }
+  return HMJ_OK;
+}
+
 extern "C" int hmj_join_strings_host(hmj_ctx* ctx, const uint64_t* h_roffsets,
                                      const uint8_t* h_rchars, size_t nr,
                                      const uint64_t* h_soffsets, const uint8_t* h_schars,

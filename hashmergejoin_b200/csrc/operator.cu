@@ -50,8 +50,11 @@ extern "C" int hmj_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr,
   hmj_relation R = {}, S = {};
   uint64_t* h = nullptr;
   uint32_t* rid = nullptr;
+  const bool skew_r = ctx->sample_skewed[0], skew_s = ctx->sample_skewed[1];
+  ctx->next_sort_skewed = skew_r;
   HMJ_TRY(sort_side_u64(ctx, d_rkeys, nr, WS_R_HASH, WS_R_ROWID, &h, &rid));
   R.d_hash = h; R.d_rowid = rid; R.n = nr; R.key_kind = HMJ_KEY_U64;
+  ctx->next_sort_skewed = skew_s;
   HMJ_TRY(sort_side_u64(ctx, d_skeys, ns, WS_S_HASH, WS_S_ROWID, &h, &rid));
   S.d_hash = h; S.d_rowid = rid; S.n = ns; S.key_kind = HMJ_KEY_U64;
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
@@ -146,7 +149,10 @@ extern "C" int hmj_join_strings_range(hmj_ctx* ctx, const uint64_t* d_roffsets, 
       return HMJ_OK;
     }
   }
+  const bool skew_r = ctx->sample_skewed[0], skew_s = ctx->sample_skewed[1];
+  ctx->next_sort_skewed = skew_r;
   HMJ_TRY(hmj_sort_pairs(ctx, rt, nullptr, nr, rh, rr));
+  ctx->next_sort_skewed = skew_s;
   HMJ_TRY(hmj_sort_pairs(ctx, st, nullptr, ns, sh, sr));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], ctx->stream));
   hmj_relation R = {rh, rr, nr, HMJ_KEY_STRING, d_roffsets, d_rchars};

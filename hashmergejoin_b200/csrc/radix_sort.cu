@@ -579,7 +579,10 @@ int hmj_impl_sort(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* vals_in
   const uint32_t seg_cap = (uint32_t)hmj_segment_sort_cap();
   // hashes with implicit row ids: try the uniform-hash path first (no histogram, no stable
   // passes); it declines or fails on skewed / heavily duplicated keys and leaves the input intact
-  if (vals_in == nullptr && hyb == 2) {
+  // (a join whose sample already found this relation skewed says so: no attempt to throw away)
+  const bool known_skewed = ctx->next_sort_skewed;
+  ctx->next_sort_skewed = false;
+  if (vals_in == nullptr && hyb == 2 && !known_skewed) {
     int ok = 0;
     HMJ_TRY(hmj_sort_uniform_try(ctx, keys_in, n, 0, keys_out, vals_out, &ok));
     if (ok) {

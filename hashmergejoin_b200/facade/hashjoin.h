@@ -25,25 +25,34 @@ typedef std::vector<std::tuple<std::size_t, std::string, uint64_t>> HashKeyValVe
 namespace hmj {
 namespace detail {
 
-// GPU join of two flattened key columns -> (build_row, probe_row) pairs.
+// GPU join of two flattened key columns -> (build_row, probe_row) pairs, received in pinned
+// arrays inside the call (the library overlaps the copies with the join, host_api.cu).
 // For kHostHash keys only hash equality is decided on the device; the caller filters by key.
 template <typename Key, typename Hash>
-void join_columns(const KeyColumns& r, const KeyColumns& s, std::vector<uint32_t>* out_r,
-                  std::vector<uint32_t>* out_s) {
+std::size_t join_columns(const KeyColumns& r, const KeyColumns& s, PinnedArray<uint32_t>* out_r,
+                         PinnedArray<uint32_t>* out_s) {
+  const double t0 = now_s();
   hmj_ctx* ctx = Context::get();
   uint64_t m = 0;
   const bool str = key_path<Key, Hash>::value == kString;
+  // room for a join with unique keys on one side; a larger result is fetched afterwards
+  const std::size_t cap = std::max(r.n, s.n);
+  out_r->resize(cap);
+  out_s->resize(cap);
+  int rc;
   if (str)
-    Context::check(hmj_join_strings_host(ctx, r.offsets.data(), r.chars.data(), r.n, s.offsets.data(),
-                                         s.chars.data(), s.n, nullptr, nullptr, 0, &m),
-                   "hmj_join_strings_host");
+    rc = hmj_join_strings_host(ctx, r.offsets.data(), r.chars.data(), r.n, s.offsets.data(),
+                               s.chars.data(), s.n, out_r->data(), out_s->data(), cap, &m);
   else
-    Context::check(hmj_join_u64_host(ctx, r.u64.data(), r.n, s.u64.data(), s.n, nullptr, nullptr, 0, &m),
-                   "hmj_join_u64_host");
-  out_r->resize(m);
-  out_s->resize(m);
-  if (m) Context::check(hmj_join_result_to_host(ctx, out_r->data(), out_s->data(), m),
-                        "hmj_join_result_to_host");
+    rc = hmj_join_u64_host(ctx, r.u64.data(), r.n, s.u64.data(), s.n, out_r->data(), out_s->data(), cap, &m);
+  if (rc == HMJ_ECAPACITY && m > cap) {
+    out_r->resize(m);
+    out_s->resize(m);
+    rc = hmj_join_result_to_host(ctx, out_r->data(), out_s->data(), m);
+  }
+  Context::check(rc, str ? "hmj_join_strings_host" : "hmj_join_u64_host");
+  stages().device_s += now_s() - t0;
+  return (std::size_t)m;
 }
 
 // The iterator both operators hand out: walks the materialised pair list.
@@ -84,22 +93,35 @@ class HashMergeJoin {
 
   HashMergeJoin() = default;
   HashMergeJoin(RIter r_begin, RIter r_end, SIter s_begin, SIter s_end,
-                unsigned int /*num_threads*/ = 1) {
+                unsigned int num_threads = 1) {
+    namespace d = hmj::detail;
+    d::stages() = d::Stages{0, 0, 0, 0};
+    const int threads = (int)(num_threads ? num_threads : 1);
     // the operator owns copies of both relations (reference: _r_sorted/_s_sorted, :62-63)
-    _r.assign(r_begin, r_end);
-    _s.assign(s_begin, s_end);
-    const hmj::detail::KeyColumns rc =
-        hmj::detail::flatten<Key, Hash>(_r.begin(), _r.end(), radix_hash::detail::first_of());
-    const hmj::detail::KeyColumns sc =
-        hmj::detail::flatten<Key, Hash>(_s.begin(), _s.end(), radix_hash::detail::first_of());
-    std::vector<uint32_t> pr, ps;
-    hmj::detail::join_columns<Key, Hash>(rc, sc, &pr, &ps);
-    const bool verify = hmj::detail::key_path<Key, Hash>::value == hmj::detail::kHostHash;
-    _rows.reserve(pr.size());
-    for (std::size_t i = 0; i < pr.size(); ++i) {
-      if (verify && !(_r[pr[i]].first == _s[ps[i]].first)) continue;
-      _rows.push_back(std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second));
+    double t0 = d::now_s();
+    copy_range(r_begin, r_end, &_r, threads);
+    copy_range(s_begin, s_end, &_s, threads);
+    d::stages().copy_s = d::now_s() - t0;
+    const d::KeyColumns rc = d::flatten<Key, Hash>(_r.begin(), _r.end(), radix_hash::detail::first_of(), threads);
+    const d::KeyColumns sc = d::flatten<Key, Hash>(_s.begin(), _s.end(), radix_hash::detail::first_of(), threads);
+    d::PinnedArray<uint32_t> pr, ps;
+    const std::size_t m = d::join_columns<Key, Hash>(rc, sc, &pr, &ps);
+    t0 = d::now_s();
+    const bool verify = d::key_path<Key, Hash>::value == d::kHostHash;
+    if (verify) {
+      _rows.reserve(m);
+      for (std::size_t i = 0; i < m; ++i) {
+        if (!(_r[pr[i]].first == _s[ps[i]].first)) continue;
+        _rows.push_back(std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second));
+      }
+    } else {
+      _rows.resize(m);
+      d::parallel_slices(m, threads, [&](int, std::size_t lo, std::size_t hi) {
+        for (std::size_t i = lo; i < hi; ++i)
+          _rows[i] = std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second);
+      });
     }
+    d::stages().rows_s = d::now_s() - t0;
   }
 
   iterator begin() { return iterator(&_rows, 0); }
@@ -111,6 +133,19 @@ class HashMergeJoin {
   }
 
  protected:
+  template <typename Iter, typename Item>
+  static void copy_range(Iter b, Iter e, std::vector<Item>* dst, int threads) {
+    if (!hmj::detail::is_random_access<Iter>::value || threads <= 1) {
+      dst->assign(b, e);
+      return;
+    }
+    const std::size_t n = (std::size_t)std::distance(b, e);
+    dst->resize(n);
+    hmj::detail::parallel_slices(n, threads, [&](int, std::size_t lo, std::size_t hi) {
+      Iter it = hmj::detail::advance_to(b, lo);
+      for (std::size_t i = lo; i < hi; ++i, ++it) (*dst)[i] = *it;
+    });
+  }
   std::vector<std::pair<Key, RValue>> _r;
   std::vector<std::pair<Key, SValue>> _s;
   std::vector<std::tuple<Key*, RValue*, SValue*>> _rows;
@@ -140,12 +175,16 @@ class HashMergeJoin2 {
     hmj::detail::KeyColumns rc, sc;
     rc.n = nr;
     sc.n = ns;
-    for (RIter it = r_begin; it != r_end; ++it) rc.u64.push_back((uint64_t)std::get<0>(*it));
-    for (SIter it = s_begin; it != s_end; ++it) sc.u64.push_back((uint64_t)std::get<0>(*it));
-    std::vector<uint32_t> pr, ps;
+    rc.u64.resize(nr);
+    sc.u64.resize(ns);
+    std::size_t k = 0;
+    for (RIter it = r_begin; it != r_end; ++it) rc.u64[k++] = (uint64_t)std::get<0>(*it);
+    k = 0;
+    for (SIter it = s_begin; it != s_end; ++it) sc.u64[k++] = (uint64_t)std::get<0>(*it);
+    hmj::detail::PinnedArray<uint32_t> pr, ps;
     struct caller_hash {};  // any non-std::hash type selects the shipped-hash (u64) path
-    hmj::detail::join_columns<Key, caller_hash>(rc, sc, &pr, &ps);
-    for (std::size_t i = 0; i < pr.size(); ++i) {
+    const std::size_t m = hmj::detail::join_columns<Key, caller_hash>(rc, sc, &pr, &ps);
+    for (std::size_t i = 0; i < m; ++i) {
       auto& r = _r_begin[pr[i]];
       auto& s = _s_begin[ps[i]];
       if (!(std::get<1>(r) == std::get<1>(s))) continue;

@@ -38,8 +38,8 @@ void partition_only(BidirectionalIterator begin, BidirectionalIterator end,
   if ((int)dst->size() < partitions) dst->resize(partitions);
   const hmj::detail::KeyColumns cols =
       hmj::detail::flatten<Key, Hash>(begin, end, hmj::detail::get0_of());
-  std::vector<uint64_t> hash;
-  std::vector<uint32_t> rowid;
+  hmj::detail::PinnedArray<uint64_t> hash;
+  hmj::detail::PinnedArray<uint32_t> rowid;
   hmj::detail::hash_sort<Key, Hash>(cols, &hash, &rowid);
   // partition sizes from the device counting kernel (reference: leader's reserve(), :62-73)
   std::vector<uint64_t> counts(partitions, 0);
@@ -67,8 +67,8 @@ void partitioned_hash_table(BidirectionalIterator begin, BidirectionalIterator e
   if ((int)tables->size() < partitions) tables->resize(partitions);
   const hmj::detail::KeyColumns cols =
       hmj::detail::flatten<Key, Hash>(begin, end, hmj::detail::get0_of());
-  std::vector<uint64_t> hash;
-  std::vector<uint32_t> rowid;
+  hmj::detail::PinnedArray<uint64_t> hash;
+  hmj::detail::PinnedArray<uint32_t> rowid;
   hmj::detail::hash_sort<Key, Hash>(cols, &hash, &rowid);
   std::vector<uint64_t> counts(partitions, 0);
   if (cols.n)

@@ -40,8 +40,8 @@ void radix_non_inplace_par(BidirectionalIterator begin, BidirectionalIterator en
                            RandomAccessIterator dst, int /*num_threads*/, int /*partition_bits*/) {
   const hmj::detail::KeyColumns cols =
       hmj::detail::flatten<Key, Hash>(begin, end, detail::first_of());
-  std::vector<uint64_t> hash;
-  std::vector<uint32_t> rowid;
+  hmj::detail::PinnedArray<uint64_t> hash;
+  hmj::detail::PinnedArray<uint32_t> rowid;
   hmj::detail::hash_sort<Key, Hash>(cols, &hash, &rowid);
   // row id -> element: bidirectional iterators are walked once into a pointer table
   typedef typename std::iterator_traits<BidirectionalIterator>::value_type Item;

@@ -187,6 +187,12 @@ int hmj_hash_sort_strings_host(hmj_ctx* ctx, const uint64_t* h_offsets, const ui
 int hmj_sort_pairs_host(hmj_ctx* ctx, const uint64_t* h_hash, const uint32_t* h_rowid, size_t n,
                         uint64_t* h_hash_out, uint32_t* h_rowid_out);
 
+/* Page-locked host memory for callers that stage columns themselves (the C++ facade flattens the
+ * caller's containers into such arrays): copies between them and the GPU run at the host link's
+ * rate and asynchronously.  No context needed. */
+int hmj_host_alloc(void** out, size_t bytes);
+int hmj_host_free(void* p);
+
 /* ---- A6: partitioning on the top hash bits ------------------------------------------- */
 /* replaces the counting loop of partition_only (partitioned_hash.h:57-60): counts[p] = number
  * of rows with (hash >> (64-bits)) == p; d_counts has 1<<bits u64 entries. bits in [1,16]. */

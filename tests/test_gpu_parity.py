@@ -735,3 +735,111 @@ def test_sort_after_release_workspace_with_scribbled_memory(ctx, oracle):
         torch.cuda.empty_cache()
         h, r = ctx.sort_pairs(dev(keys))
         assert np.array_equal(host(h, np.uint64), want_h) and np.array_equal(host(r, np.uint32), want_r)
+
+
+# ------------------------------------------------------------------ plan selection by sampling
+def _check_pairs_1to1(rk, sk, out_r, out_s):
+    assert out_r.size == rk.size
+    assert np.array_equal(rk[out_r], sk[out_s])
+    assert np.array_equal(np.sort(out_r), np.arange(rk.size, dtype=np.uint32))
+    assert np.array_equal(np.sort(out_s), np.arange(sk.size, dtype=np.uint32))
+
+
+def test_join_dense_integer_keys_take_the_bucket_path(ctx):
+    # identity hash of keys 0..N-1: the upper 64 - log2(N) hash bits are all zero.  The sample finds
+    # the shared prefix, the plan skips it, level 1 checks it on every row.
+    n = 1 << 23
+    rng = np.random.default_rng(3)
+    rk, sk = rng.permutation(n).astype(np.uint64), rng.permutation(n).astype(np.uint64)
+    m = ctx.join_u64(dev(rk), dev(sk))
+    tm = ctx.timings()
+    assert tm["bucket_join"] == 1 and tm["sort_passes"] == 0, "dense keys did not take the bucket path"
+    _check_pairs_1to1(rk, sk, *ctx.join_result_to_host(m))
+    # the same keys behind a constant offset that leaves a common prefix
+    off = np.uint64(0xABCD) << np.uint64(40)
+    m = ctx.join_u64(dev(rk + off), dev(sk + off))
+    assert ctx.timings()["bucket_join"] == 1
+    _check_pairs_1to1(rk, sk, *ctx.join_result_to_host(m))
+    # one row the sample does not see breaks the prefix: the attempt is void, the result is not
+    rk2 = rk.copy()
+    rk2[12345] = np.uint64(1) << np.uint64(63)
+    m = ctx.join_u64(dev(rk2), dev(sk))
+    assert ctx.timings()["bucket_join"] == 0
+    out_r, out_s = ctx.join_result_to_host(m)
+    assert m == n - 1 and np.array_equal(rk2[out_r], sk[out_s])
+    assert np.unique(out_r).size == n - 1
+
+
+def test_join_skewed_keys_skip_the_scatter_attempt(ctx, oracle):
+    # a Zipf-distributed integer relation: the sample sees the head key's region at several times
+    # its share, so no bucket scatter is attempted at all
+    n = 1 << 22
+    keys = datagen.unique_u64(1 << 16, seed=4)
+    rk = keys[datagen.zipf_ranks(datagen.zipf_cdf(keys.size), n, 3).astype(np.int64)]
+    sk = datagen.permuted(np.concatenate([keys] * 2), 5)
+    m = ctx.join_u64(dev(rk), dev(sk))
+    tm = ctx.timings()
+    # (the uniform relation S is still sorted by its own two scatter levels; R goes straight to the
+    # histogram-planned stable passes)
+    assert tm["bucket_join"] == 0 and tm["scatter_levels"] <= 2 and tm["sort_fallbacks"] == 0, \
+        "a scatter attempt was thrown away on a relation the sample had found skewed"
+    assert m == 2 * n
+    out_r, out_s = ctx.join_result_to_host(m)
+    assert np.array_equal(rk[out_r], sk[out_s])
+    w = (out_r.astype(np.uint64) << np.uint64(32)) | out_s.astype(np.uint64)
+    assert np.unique(w).size == m
+
+
+def test_join_order_option_gives_hash_order_reproducibly(ctx, oracle):
+    n = 300000
+    keys = datagen.unique_u64(n, seed=8)
+    rk, sk = datagen.permuted(keys, 1).copy(), datagen.permuted(keys, 2).copy()
+    sk[:5000] = sk[5000:10000]   # duplicates on the probe side
+    runs = []
+    ctx.set_join_order(True)
+    try:
+        for _ in range(2):
+            m = ctx.join_u64(dev(rk), dev(sk))
+            assert ctx.timings()["bucket_join"] == 0
+            runs.append(ctx.join_result_to_host(m))
+    finally:
+        ctx.set_join_order(False)
+    (a_r, a_s), (b_r, b_s) = runs
+    assert np.array_equal(a_r, b_r) and np.array_equal(a_s, b_s), "hash order is not reproducible"
+    h = rk[a_r]
+    assert np.all(h[1:] >= h[:-1]), "pairs are not in ascending hash order"
+    t_r, t_s, _ = oracle.full_join(Keys(u64=rk), Keys(u64=sk))
+    c_r, c_s = oracle.sort_pairs(a_r, a_s)
+    assert np.array_equal(c_r, t_r) and np.array_equal(c_s, t_s)
+    m = ctx.join_u64(dev(rk), dev(sk))
+    assert ctx.timings()["bucket_join"] == 1, "the default order must take the faster plan again"
+
+
+def test_host_join_in_chunks_and_its_fallbacks(ctx, oracle):
+    # hmj_join_u64_host copies R in chunks, joins every chunk against S's buckets and sends the
+    # pairs home while the next chunk arrives; the union is the join
+    n = 3 << 20
+    keys = datagen.unique_u64(n, seed=12)
+    rk, sk = datagen.permuted(keys, 1).copy(), datagen.permuted(keys, 2).copy()
+    out_r, out_s = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+    assert ctx.join_u64_host(rk, sk, out_r, out_s) == n
+    assert ctx.timings()["bucket_join"] == 1 and ctx.timings()["scatter_levels"] > 4, "not the chunked plan"
+    _check_pairs_1to1(rk, sk, out_r, out_s)
+    # R much smaller than S and the other way round
+    for a, b in ((rk[: n // 5], sk), (rk, sk[: n // 7])):
+        o_r, o_s = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        m = ctx.join_u64_host(a, b, o_r, o_s)
+        assert m == min(a.size, b.size) and np.array_equal(a[o_r[:m]], b[o_s[:m]])
+        assert np.unique(o_r[:m]).size == m
+    # every key three times on the probe side: 3n pairs do not fit the first guess, the plain path
+    # re-runs with the exact size
+    sk3 = datagen.permuted(np.concatenate([sk, sk, sk]), 9)
+    o_r, o_s = np.zeros(3 * n, np.uint32), np.zeros(3 * n, np.uint32)
+    assert ctx.join_u64_host(rk, sk3, o_r, o_s) == 3 * n
+    assert np.array_equal(rk[o_r], sk3[o_s])
+    w = (o_r.astype(np.uint64) << np.uint64(32)) | o_s.astype(np.uint64)
+    assert np.unique(w).size == 3 * n
+    # a capacity that is too small is reported, with the number of pairs
+    with pytest.raises(hmj.HmjError) as ei:
+        ctx.join_u64_host(rk, sk, out_r[: n // 2], out_s[: n // 2])
+    assert ei.value.code == -5
