@@ -41,7 +41,7 @@ oracle/_ref/libhmj_ref.so: oracle/ref_shim.cc
 
 # ---- C++ facade tests (mirror the reference's gtest files against the facade headers) --
 FACADE    := hashmergejoin_b200/facade
-TEST_BINS := $(BUILD)/facade_test $(BUILD)/facade_bench
+TEST_BINS := $(BUILD)/facade_test $(BUILD)/facade_bench $(BUILD)/facade_bench_borrow
 tests: $(TEST_BINS)
 $(BUILD)/facade_test: tests/cpp/facade_test.cc $(wildcard $(FACADE)/*.h) include/hmj.h $(LIB)
 	@mkdir -p $(BUILD)
@@ -51,6 +51,11 @@ $(BUILD)/facade_test: tests/cpp/facade_test.cc $(wildcard $(FACADE)/*.h) include
 $(BUILD)/facade_bench: tests/cpp/facade_bench.cc $(wildcard $(FACADE)/*.h) include/hmj.h $(LIB)
 	@mkdir -p $(BUILD)
 	$(CXX) -O2 -std=c++11 -pthread -Iinclude -I$(FACADE) -o $@ tests/cpp/facade_bench.cc \
+	    -Lhashmergejoin_b200 -lhmj -Wl,-rpath,'$$ORIGIN/../hashmergejoin_b200'
+
+$(BUILD)/facade_bench_borrow: tests/cpp/facade_bench.cc $(wildcard $(FACADE)/*.h) include/hmj.h $(LIB)
+	@mkdir -p $(BUILD)
+	$(CXX) -O2 -std=c++11 -pthread -DHMJ_FACADE_BORROW_INPUTS -Iinclude -I$(FACADE) -o $@ tests/cpp/facade_bench.cc \
 	    -Lhashmergejoin_b200 -lhmj -Wl,-rpath,'$$ORIGIN/../hashmergejoin_b200'
 
 clean:

@@ -9,6 +9,7 @@
 // hash hit.  Algorithmic bytes: build reads 8 (+key) per row and touches one 16 B slot;
 // probe reads 8 (+key) per row and >= one 32 B sector.
 #include "common.cuh"
+#include "join_device.cuh"
 
 namespace {
 
@@ -39,17 +40,11 @@ struct HtArgs {
   uint64_t* out;           // [0] hits, [1] sum
 };
 
-__device__ __forceinline__ bool bytes_equal(const uint8_t* a, const uint8_t* b, uint64_t len) {
-  for (uint64_t i = 0; i < len; ++i)
-    if (a[i] != b[i]) return false;
-  return true;
-}
-
+// full-key check of a slot whose hash matched: the word-wise comparison the join kernels use
+// (join_device.cuh), 8 key bytes per step whatever the two keys' alignment
 __device__ __forceinline__ bool str_rows_equal(const uint64_t* aoff, const uint8_t* ac, uint32_t ar,
                                                const uint64_t* boff, const uint8_t* bc, uint32_t br) {
-  const uint64_t a0 = aoff[ar], la = aoff[ar + 1] - a0;
-  const uint64_t b0 = boff[br], lb = boff[br + 1] - b0;
-  return la == lb && bytes_equal(ac + a0, bc + b0, la);
+  return keys_equal_str(aoff, ac, ar, boff, bc, br);
 }
 
 __device__ __forceinline__ uint32_t wait_row(const HtSlot* s) {

@@ -60,19 +60,17 @@ template <typename Key, typename RValue, typename SValue>
 class JoinCursor : public std::iterator<std::input_iterator_tag, std::tuple<Key*, RValue*, SValue*>> {
  public:
   typedef std::tuple<Key*, RValue*, SValue*> value_type;
-  JoinCursor(const std::vector<value_type>* rows, std::size_t pos) : rows_(rows), pos_(pos) { load(); }
-  JoinCursor& operator++() { ++pos_; load(); return *this; }
+  JoinCursor(value_type* rows, std::size_t pos) : rows_(rows), pos_(pos) {}
+  JoinCursor& operator++() { ++pos_; return *this; }
   JoinCursor operator++(int) { JoinCursor t(*this); ++*this; return t; }
   bool operator==(const JoinCursor& o) const { return pos_ == o.pos_; }
   bool operator!=(const JoinCursor& o) const { return pos_ != o.pos_; }
-  value_type& operator*() { return cur_; }
-  value_type* operator->() { return &cur_; }
+  value_type& operator*() { return rows_[pos_]; }
+  value_type* operator->() { return rows_ + pos_; }
 
  private:
-  void load() { if (rows_ && pos_ < rows_->size()) cur_ = (*rows_)[pos_]; }
-  const std::vector<value_type>* rows_;
+  value_type* rows_;
   std::size_t pos_;
-  value_type cur_;
 };
 
 }  // namespace detail
@@ -97,58 +95,75 @@ class HashMergeJoin {
     namespace d = hmj::detail;
     d::stages() = d::Stages{0, 0, 0, 0};
     const int threads = (int)(num_threads ? num_threads : 1);
-    // the operator owns copies of both relations (reference: _r_sorted/_s_sorted, :62-63)
+    // The operator owns copies of both relations, as the reference's does (_r_sorted/_s_sorted,
+    // :62-63): dereferenced pointers stay valid when the caller's containers go away.  Callers
+    // whose inputs outlive the operator can compile with -DHMJ_FACADE_BORROW_INPUTS and skip it
+    // (random-access inputs only; for std::string keys the copy is most of the host time).
     double t0 = d::now_s();
-    copy_range(r_begin, r_end, &_r, threads);
-    copy_range(s_begin, s_end, &_s, threads);
+    copy_range(r_begin, r_end, &_r, &_r_data, threads);
+    copy_range(s_begin, s_end, &_s, &_s_data, threads);
     d::stages().copy_s = d::now_s() - t0;
-    const d::KeyColumns rc = d::flatten<Key, Hash>(_r.begin(), _r.end(), radix_hash::detail::first_of(), threads);
-    const d::KeyColumns sc = d::flatten<Key, Hash>(_s.begin(), _s.end(), radix_hash::detail::first_of(), threads);
+    const std::size_t nr = (std::size_t)std::distance(r_begin, r_end), ns = (std::size_t)std::distance(s_begin, s_end);
+    const d::KeyColumns rc = d::flatten<Key, Hash>(_r_data, _r_data + nr, radix_hash::detail::first_of(), threads);
+    const d::KeyColumns sc = d::flatten<Key, Hash>(_s_data, _s_data + ns, radix_hash::detail::first_of(), threads);
     d::PinnedArray<uint32_t> pr, ps;
     const std::size_t m = d::join_columns<Key, Hash>(rc, sc, &pr, &ps);
     t0 = d::now_s();
     const bool verify = d::key_path<Key, Hash>::value == d::kHostHash;
+    std::pair<Key, RValue>* R = _r_data;
+    std::pair<Key, SValue>* S = _s_data;
     if (verify) {
-      _rows.reserve(m);
-      for (std::size_t i = 0; i < m; ++i) {
-        if (!(_r[pr[i]].first == _s[ps[i]].first)) continue;
-        _rows.push_back(std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second));
-      }
+      // hashes of a user functor can collide: keep the pairs whose keys are equal
+      std::vector<uint32_t> keep;
+      for (std::size_t i = 0; i < m; ++i)
+        if (R[pr[i]].first == S[ps[i]].first) keep.push_back((uint32_t)i);
+      _rows.build(keep.size(), threads, [&](std::size_t k) {
+        const std::size_t i = keep[k];
+        return std::make_tuple(&R[pr[i]].first, &R[pr[i]].second, &S[ps[i]].second);
+      });
     } else {
-      _rows.resize(m);
-      d::parallel_slices(m, threads, [&](int, std::size_t lo, std::size_t hi) {
-        for (std::size_t i = lo; i < hi; ++i)
-          _rows[i] = std::make_tuple(&_r[pr[i]].first, &_r[pr[i]].second, &_s[ps[i]].second);
+      _rows.build(m, threads, [&](std::size_t i) {
+        return std::make_tuple(&R[pr[i]].first, &R[pr[i]].second, &S[ps[i]].second);
       });
     }
     d::stages().rows_s = d::now_s() - t0;
   }
 
-  iterator begin() { return iterator(&_rows, 0); }
-  iterator end() { return iterator(&_rows, _rows.size()); }
+  iterator begin() { return iterator(_rows.begin(), 0); }
+  iterator end() { return iterator(_rows.begin(), _rows.size()); }
   void clear() {
     _rows.clear();
     _r.clear();
     _s.clear();
+    _r_data = nullptr;
+    _s_data = nullptr;
   }
 
  protected:
   template <typename Iter, typename Item>
-  static void copy_range(Iter b, Iter e, std::vector<Item>* dst, int threads) {
-    if (!hmj::detail::is_random_access<Iter>::value || threads <= 1) {
-      dst->assign(b, e);
+  static void copy_range(Iter b, Iter e, hmj::detail::ParallelArray<Item>* own, Item** data, int threads) {
+    const std::size_t n = (std::size_t)std::distance(b, e);
+#ifdef HMJ_FACADE_BORROW_INPUTS
+    if (hmj::detail::is_random_access<Iter>::value && n) {
+      *data = const_cast<Item*>(&*b);
       return;
     }
-    const std::size_t n = (std::size_t)std::distance(b, e);
-    dst->resize(n);
-    hmj::detail::parallel_slices(n, threads, [&](int, std::size_t lo, std::size_t hi) {
-      Iter it = hmj::detail::advance_to(b, lo);
-      for (std::size_t i = lo; i < hi; ++i, ++it) (*dst)[i] = *it;
-    });
+#endif
+    if (hmj::detail::is_random_access<Iter>::value) {
+      own->build(n, threads, [&](std::size_t i) { return *hmj::detail::advance_to(b, i); });
+    } else {
+      std::vector<const Item*> at;
+      at.reserve(n);
+      for (Iter it = b; it != e; ++it) at.push_back(&*it);
+      own->build(n, threads, [&](std::size_t i) { return *at[i]; });
+    }
+    *data = own->begin();
   }
-  std::vector<std::pair<Key, RValue>> _r;
-  std::vector<std::pair<Key, SValue>> _s;
-  std::vector<std::tuple<Key*, RValue*, SValue*>> _rows;
+  hmj::detail::ParallelArray<std::pair<Key, RValue>> _r;
+  hmj::detail::ParallelArray<std::pair<Key, SValue>> _s;
+  std::pair<Key, RValue>* _r_data = nullptr;
+  std::pair<Key, SValue>* _s_data = nullptr;
+  hmj::detail::ParallelArray<std::tuple<Key*, RValue*, SValue*>> _rows;
 };
 
 // Pre-hashed tuples (hash, key, value) owned by the caller; both ranges are sorted in place on
@@ -192,8 +207,8 @@ class HashMergeJoin2 {
     }
   }
 
-  iterator begin() { return iterator(&_rows, 0); }
-  iterator end() { return iterator(&_rows, _rows.size()); }
+  iterator begin() { return iterator(_rows.data(), 0); }
+  iterator end() { return iterator(_rows.data(), _rows.size()); }
   void clear() { _rows.clear(); }
 
  protected:
