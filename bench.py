@@ -704,6 +704,10 @@ def run_gpu_strings(args, wl):
     ms_per_step = elapsed_ms / args.steps
     units = rows_total if kind == "sort" else 2 * rows_total
     value = units / (ms_per_step * 1e-3)
+    if world == 1:
+        # the library books 16 B per row for hash_strings_kernel (offset read + hash written); the key
+        # bytes it also reads are known here: every step hashes every key once
+        tm["kernel_bytes"][5] += float(key_bytes) * args.steps
     roofline, kernels = roofline_from(tm, elapsed_ms)
 
     # ---- verification on the device

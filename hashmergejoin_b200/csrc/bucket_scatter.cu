@@ -149,25 +149,17 @@ bucket_scatter_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __re
 // load latency: profiles/r1d, 54 % of its stall samples).  The tile is permuted in place in its
 // buffer and leaves with coalesced stores.
 constexpr int UT_ITEMS = 8;
-// RANK: how an item gets its slot inside its digit's run of the tile.
-//   0  one shared-memory atomicAdd per item on the tile's digit counters.  ATOMS on spread
-//      addresses is served lane by lane (~0.6 cycles per lane measured here; the LSU pipe was the
-//      kernel's limiter at 70 % wavefront utilisation, about half of it these atomics).
-//   1  warp-private digit counters (u16, [warps][256]) and a warp-level multisplit: lanes with
-//      the same digit find each other with match.any, take their rank from the lane mask, the
-//      group's first lane bumps the warp's counter with a plain load + store; a column scan over
-//      the warps then gives every warp its base inside the digit's run.  No shared-memory atomics.
-//   2  as 1 with the peer mask built from one ballot per digit bit instead of match.any.
-// 1 and 2 need bins <= 256 (the 512-thread configurations); the 9-bit levels keep 0.
-template <int THREADS, int RANK>
+// (Measured and removed in round 2: ranking a tile's items with a warp-level multisplit --
+// match.any, or one ballot per digit bit -- on warp-private u16 counters instead of one
+// shared-memory atomicAdd per item: 2.66 ms / 2.33 ms per 256M-pair launch against 1.35 ms.  The
+// dependent load-store chain per item costs more than the atomics' LSU time.)
+template <int THREADS>
 struct UtCfg {
   static constexpr int TILE = THREADS * UT_ITEMS;
-  static constexpr int WARPS = THREADS / 32;
   static constexpr int BINS = THREADS > 512 ? 512 : 256;   // most bins a level of this shape cuts
   static constexpr size_t BUF_BYTES = (size_t)TILE * 12;
-  static constexpr size_t WCNT_BYTES = RANK ? (size_t)WARPS * 256 * 2 : 0;
-  // buffers, [cnt][off][gbase] per bin, region counts (<= 512), warp counters, scan, bars, peers
-  static constexpr size_t SMEM = 2 * BUF_BYTES + 3 * BINS * 4 + 512 * 4 + WCNT_BYTES + 32 * 4 + 64 + 16 * 8;
+  // buffers, [cnt][off][gbase] per bin, region ends and starts (<= 512 regions), scan, bars, peers
+  static constexpr size_t SMEM = 2 * BUF_BYTES + 3 * BINS * 4 + 2 * 512 * 4 + 32 * 4 + 64 + 16 * 8;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -211,27 +203,31 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
 // serialise at ~30 ns each and bound the first version of this kernel at 240 GB/s of NVLink).
 // region_shift (level 2 of such a job): input region t / tiles_per_region is a sub-region; the
 // bucket prefix is the region it belongs to, (t / tiles_per_region) >> region_shift.
-
-template <int UT_THREADS, int MIN_BLOCKS, bool DIST, int RANK>
+// in_starts (the multi-GPU join takes a relation in parts): input region r holds the pairs
+// [in_starts[r], in_counts[r]); earlier parts of the region were processed by an earlier launch.
+// The first tile of a region then starts at in_starts[r] rounded down to 4 pairs (bulk copies need
+// 16-byte aligned sources) and ignores the `lo` pairs before the start.
+// STARTS = false compiles the region starts out (every level but the local ones of the multi-GPU join)
+template <int UT_THREADS, int MIN_BLOCKS, bool DIST, bool STARTS>
 __global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
 bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                          const uint32_t* __restrict__ in_counts, uint32_t in_stride,
-                          uint32_t n_single, uint32_t tiles_per_region, uint32_t total_tiles,
-                          uint32_t iota_base, uint64_t* __restrict__ keys_out,
+                          const uint32_t* __restrict__ in_counts, const uint32_t* __restrict__ in_starts,
+                          uint32_t in_stride, uint32_t n_single, uint32_t tiles_per_region,
+                          uint32_t total_tiles, uint32_t iota_base, uint64_t* __restrict__ keys_out,
                           uint32_t* __restrict__ vals_out, int shift, int bits, uint32_t out_cap,
                           uint32_t* __restrict__ cursors, uint32_t* __restrict__ flag,
                           uint32_t* __restrict__ tile_counter, const hmj_peer_regions peers,
                           int region_shift, uint64_t prefix, int prefix_bits) {
-  using Cfg = UtCfg<UT_THREADS, RANK>;
+  using Cfg = UtCfg<UT_THREADS>;
   constexpr int UT_TILE = Cfg::TILE;
   constexpr size_t UT_BUF_BYTES = Cfg::BUF_BYTES;
   extern __shared__ __align__(128) unsigned char smem_tma[];
   uint32_t* s_cnt = reinterpret_cast<uint32_t*>(smem_tma + 2 * UT_BUF_BYTES);
   uint32_t* s_off = s_cnt + Cfg::BINS;
   uint32_t* s_gbase = s_off + Cfg::BINS;
-  uint32_t* s_rcount = s_gbase + Cfg::BINS;    // [regions <= 512] pairs per input region
-  uint16_t* s_wcnt = reinterpret_cast<uint16_t*>(s_rcount + 512);  // [warps][256] (RANK != 0)
-  uint32_t* s_scan = reinterpret_cast<uint32_t*>(reinterpret_cast<unsigned char*>(s_wcnt) + Cfg::WCNT_BYTES);  // [32]
+  uint32_t* s_rcount = s_gbase + Cfg::BINS;    // [regions <= 512] end of the pairs of an input region
+  uint32_t* s_rstart = s_rcount + 512;         // [regions <= 512] ... and their start
+  uint32_t* s_scan = s_rstart + 512;           // [32]
   uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_scan + 32);  // [2]
   uint64_t** s_pk = reinterpret_cast<uint64_t**>(s_bar + 2);   // [8] peer key columns (DIST)
   uint32_t** s_pv = reinterpret_cast<uint32_t**>(s_pk + 8);    // [8] peer row-id columns
@@ -260,26 +256,31 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
   }
   if (in_counts) {
     const uint32_t regions = (total_tiles + tiles_per_region - 1) / tiles_per_region;
-    for (uint32_t r = tid; r < regions; r += UT_THREADS)
+    for (uint32_t r = tid; r < regions; r += UT_THREADS) {
       s_rcount[r] = min(in_counts[r * US_CURSOR_STRIDE], in_stride);
+      if (STARTS) s_rstart[r] = min(in_starts[r * US_CURSOR_STRIDE], in_stride);
+    }
   }
   __syncthreads();
 
-  // tile t -> (region, first pair, number of pairs); 0 pairs = nothing there
-  auto tile_of = [&](uint32_t t, uint32_t* in_base) -> uint32_t {
+  // tile t -> (first slot, pairs to ignore at its head, end of its pairs); 0 = nothing there
+  auto tile_of = [&](uint32_t t, uint32_t* in_base, uint32_t* lo) -> uint32_t {
     const uint32_t r = t / tiles_per_region, j = t % tiles_per_region;
     const uint32_t count = in_counts ? s_rcount[r] : n_single;
-    const uint64_t first = (uint64_t)j * UT_TILE;
+    const uint32_t start = (STARTS && in_counts) ? s_rstart[r] : 0u;
+    const uint32_t aligned = start & ~3u;
+    const uint64_t first = (uint64_t)aligned + (uint64_t)j * UT_TILE;
     if (first >= count) return 0;
     *in_base = r * in_stride + (uint32_t)first;
+    *lo = (STARTS && j == 0) ? start - aligned : 0u;
     return (uint32_t)min((uint64_t)UT_TILE, count - first);
   };
   // Starts the copies of tile t into buffer b (full tiles only; a partial tile is loaded with
   // plain loads when its turn comes).  Every thread learns whether a copy is in flight, thread 0
   // issues it.
   auto issue = [&](uint32_t t, int b) -> bool {
-    uint32_t in_base = 0;
-    const uint32_t valid = t < total_tiles ? tile_of(t, &in_base) : 0;
+    uint32_t in_base = 0, lo = 0;
+    const uint32_t valid = t < total_tiles ? tile_of(t, &in_base, &lo) : 0;
     if (valid != (uint32_t)UT_TILE) return false;
     if (tid == 0) {
       unsigned char* buf = smem_tma + (size_t)b * UT_BUF_BYTES;
@@ -302,9 +303,10 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     pending_next = issue(t_next, b ^ 1);
     uint32_t fetched = 0;
     if (tid == 0) fetched = atomicAdd(tile_counter, 1u);
-    uint32_t in_base = 0;
-    const uint32_t valid = tile_of(t, &in_base);
-    if (valid == 0) {
+    uint32_t in_base = 0, lo_rt = 0;
+    const uint32_t valid = tile_of(t, &in_base, &lo_rt);
+    const uint32_t lo = STARTS ? lo_rt : 0u;
+    if (valid <= lo) {
       if (tid == 0) s_next[b] = fetched;
       __syncthreads();
       t = t_next;
@@ -319,12 +321,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     }
     uint64_t* b_keys = reinterpret_cast<uint64_t*>(smem_tma + (size_t)b * UT_BUF_BYTES);
     uint32_t* b_vals = reinterpret_cast<uint32_t*>(b_keys + UT_TILE);
-    if (RANK == 0) {
-      if (tid < bins) s_cnt[tid] = 0;
-    } else {
-      // the warp's own counters (256 x u16 = 512 bytes: one 16-byte store per lane)
-      reinterpret_cast<uint4*>(s_wcnt + warp * 256)[lane] = make_uint4(0, 0, 0, 0);
-    }
+    if (tid < bins) s_cnt[tid] = 0;
     if (pending_cur) {
       mbar_wait(&s_bar[b], phase[b]);
       phase[b] ^= 1;
@@ -336,67 +333,23 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     }
     __syncthreads();
 
-    uint64_t key[UT_ITEMS];
-    uint16_t slot[UT_ITEMS];
     // prefix_bits > 0 (first level of a plan that skips the hash bits all rows were found to share
     // in a sample): a row with other top bits would land in a wrong bucket -- it voids the attempt
     bool stray = false;
-    if (RANK == 0) {
+    uint64_t key[UT_ITEMS];
+    uint16_t slot[UT_ITEMS];
 #pragma unroll
-      for (int k = 0; k < UT_ITEMS; ++k) {
-        const uint32_t i = tid + k * UT_THREADS;
-        if (i < valid) {
-          key[k] = b_keys[i];
-          slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
-          if (prefix_bits) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
-        }
-      }
-    } else {
-      uint16_t* wc = s_wcnt + warp * 256;
-      const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll
-      for (int k = 0; k < UT_ITEMS; ++k) {
-        const uint32_t i = tid + k * UT_THREADS;
-        const bool live = i < valid;
-        key[k] = live ? b_keys[i] : 0;
-        // rows past the end of a partial tile share the digit 256, which no counter holds
-        const uint32_t dig = live ? (uint32_t)(key[k] >> shift) & mask : 256u;
-        if (prefix_bits && live) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
-        uint32_t peers_of;
-        if (RANK == 1) {
-          peers_of = __match_any_sync(0xffffffffu, dig);
-        } else {
-          peers_of = 0xffffffffu;
-#pragma unroll
-          for (int bit = 0; bit < 9; ++bit) {
-            const bool one = (dig >> bit) & 1u;
-            const uint32_t bl = __ballot_sync(0xffffffffu, one);
-            peers_of &= one ? bl : ~bl;
-          }
-        }
-        const uint32_t rank = __popc(peers_of & lt);
-        uint32_t base = 0;
-        if (live) base = wc[dig];
-        __syncwarp();
-        if (live && rank == 0) wc[dig] = (uint16_t)(base + __popc(peers_of));
-        __syncwarp();
-        slot[k] = (uint16_t)(base + rank);
+    for (int k = 0; k < UT_ITEMS; ++k) {
+      const uint32_t i = tid + k * UT_THREADS;
+      if (i >= lo && i < valid) {
+        key[k] = b_keys[i];
+        slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
+        if (prefix_bits) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
       }
     }
     __syncthreads();
 
     uint32_t c = 0, old = 0, bucket = 0;
-    if (RANK != 0 && tid < bins) {
-      // column scan: warp w's base inside the digit's run = pairs of the warps before it
-      uint32_t run = 0;
-#pragma unroll
-      for (int w = 0; w < Cfg::WARPS; ++w) {
-        const uint32_t x = s_wcnt[w * 256 + tid];
-        s_wcnt[w * 256 + tid] = (uint16_t)run;
-        run += x;
-      }
-      s_cnt[tid] = run;
-    }
     if (tid < bins) {
       c = s_cnt[tid];
       bucket = (((t / tiles_per_region) >> region_shift) << bits) | (uint32_t)tid;
@@ -408,7 +361,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
-      if (i < valid) val[k] = vals_in ? b_vals[i] : in_base + i + iota_base;
+      if (i >= lo && i < valid) val[k] = vals_in ? b_vals[i] : in_base + i + iota_base;
     }
     {
       uint32_t x = c;
@@ -419,27 +372,18 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       }
       if (lane == 31) s_scan[warp] = x;
       __syncthreads();
-      uint32_t wt = lane < warp ? s_scan[lane] : 0;  // 16 warps
+      uint32_t wt = lane < warp ? s_scan[lane] : 0;  // <= 32 warps
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
-      if (tid < bins) {
-        const uint32_t off = wt + x - c;
-        s_off[tid] = off;
-        if (RANK != 0) {
-          // fold the digit's start into the warps' bases: one lookup per item below
-#pragma unroll
-          for (int w = 0; w < Cfg::WARPS; ++w) s_wcnt[w * 256 + tid] += (uint16_t)off;
-        }
-      }
+      if (tid < bins) s_off[tid] = wt + x - c;
     }
     __syncthreads();  // s_off ready; every thread holds its keys and row ids in registers
 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
-      if (i < valid) {
-        const uint32_t d = (uint32_t)(key[k] >> shift) & mask;
-        const uint32_t p = (RANK == 0 ? s_off[d] : (uint32_t)s_wcnt[warp * 256 + d]) + slot[k];
+      if (i >= lo && i < valid) {
+        const uint32_t p = s_off[(uint32_t)(key[k] >> shift) & mask] + slot[k];
         b_keys[p] = key[k];
         b_vals[p] = val[k];
       }
@@ -454,8 +398,9 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       if (pending_next) mbar_wait(&s_bar[b ^ 1], phase[b ^ 1]);
       return;
     }
+    const uint32_t live = valid - lo;  // the permuted pairs sit at [0, live)
 #pragma unroll 4
-    for (uint32_t i = tid; i < valid; i += UT_THREADS) {
+    for (uint32_t i = tid; i < live; i += UT_THREADS) {
       const uint64_t kk = b_keys[i];
       const uint32_t d = (uint32_t)(kk >> shift) & mask;
       const uint32_t dst = s_gbase[d] + i;
@@ -475,13 +420,13 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
   }
 }
 
-// after the DIST level 1: region r's count of THIS source goes to the owner's count table
+// after a DIST level 1: this source's cursor of region r goes to the owner's count table `part`
 __global__ void push_counts_kernel(const uint32_t* __restrict__ cursors, uint32_t regions,
-                                   const hmj_peer_regions peers) {
+                                   const hmj_peer_regions peers, uint32_t table_offset) {
   const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= regions) return;
   const uint32_t local = r & ((1u << peers.own_bits) - 1);
-  peers.counts[r >> peers.own_bits][local * (uint32_t)peers.world + (uint32_t)peers.rank] = cursors[r];
+  peers.counts[r >> peers.own_bits][table_offset + local * (uint32_t)peers.world + (uint32_t)peers.rank] = cursors[r];
 }
 
 // exclusive scan of the final bucket counts -> dense output offsets (one CTA; <= 2^18 buckets)
@@ -525,19 +470,9 @@ int uniform_from_env() {
   return e ? atoi(e) : 1;
 }
 
-// HMJ_SCATTER_RANK: 0 = shared-memory atomics (default), 1 = match.any multisplit, 2 = ballot
-// multisplit (see UtCfg).  Measured on C3 (256M pairs per launch): 1.35 / 2.66 / 2.33 ms.
-int rank_from_env() {
-  static const int v = [] {
-    const char* e = getenv("HMJ_SCATTER_RANK");
-    const int r = e ? atoi(e) : 0;
-    return r < 0 || r > 2 ? 0 : r;
-  }();
-  return v;
-}
-
 struct ScatterLaunch {
   const uint64_t* keys_in; const uint32_t* vals_in; const uint32_t* in_counts;
+  const uint32_t* in_starts;                // != nullptr: region r holds [in_starts[r], in_counts[r])
   uint32_t in_stride, n_single, tiles_per_region, total_tiles, iota_base;
   uint64_t* keys_out; uint32_t* vals_out;
   int shift, bits;
@@ -549,18 +484,18 @@ struct ScatterLaunch {
   int prefix_bits;
 };
 
-template <int T, int B, bool DIST, int RANK>
+template <int T, int B, bool DIST, bool STARTS>
 int launch_tma(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
-  using Cfg = UtCfg<T, RANK>;
+  using Cfg = UtCfg<T>;
   static_assert(Cfg::SMEM * B + 1024 * B <= 233472, "scatter configuration does not fit an SM");
-  auto* kern = bucket_scatter_tma_kernel<T, B, DIST, RANK>;
+  auto* kern = bucket_scatter_tma_kernel<T, B, DIST, STARTS>;
   HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
   const uint32_t per_sm = ctas_per_sm == 0 || ctas_per_sm > (uint32_t)B ? (uint32_t)B : ctas_per_sm;
   const uint32_t grid = std::min(a.total_tiles, (uint32_t)ctx->num_sms * per_sm);
-  kern<<<grid, T, Cfg::SMEM, st>>>(a.keys_in, a.vals_in, a.in_counts, a.in_stride, a.n_single,
-                                   a.tiles_per_region, a.total_tiles, a.iota_base, a.keys_out,
-                                   a.vals_out, a.shift, a.bits, a.out_cap, a.cursors, a.flag,
-                                   a.tile_counter, a.peers ? *a.peers : hmj_peer_regions(),
+  kern<<<grid, T, Cfg::SMEM, st>>>(a.keys_in, a.vals_in, a.in_counts, a.in_starts, a.in_stride,
+                                   a.n_single, a.tiles_per_region, a.total_tiles, a.iota_base,
+                                   a.keys_out, a.vals_out, a.shift, a.bits, a.out_cap, a.cursors,
+                                   a.flag, a.tile_counter, a.peers ? *a.peers : hmj_peer_regions(),
                                    a.region_shift, a.prefix, a.prefix_bits);
   HMJ_LAUNCHED(ctx);
   ctx->tm.scatter_levels++;
@@ -574,20 +509,15 @@ uint32_t tile_items_for(int bits) { return bits > 8 ? 8192u : 4096u; }
 int launch_scatter(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
   if (a.total_tiles == 0) return HMJ_OK;
   const bool dist = a.peers != nullptr;
-  if (a.bits > 8)  // 512 bins: 1024-thread tiles of 8192 pairs, shared-memory atomics
-    return dist ? launch_tma<1024, 1, true, 0>(ctx, a, ctas_per_sm, st)
-                : launch_tma<1024, 1, false, 0>(ctx, a, ctas_per_sm, st);
-  switch (rank_from_env()) {
-    case 0:
-      return dist ? launch_tma<512, 2, true, 0>(ctx, a, ctas_per_sm, st)
-                  : launch_tma<512, 2, false, 0>(ctx, a, ctas_per_sm, st);
-    case 2:
-      return dist ? launch_tma<512, 2, true, 2>(ctx, a, ctas_per_sm, st)
-                  : launch_tma<512, 2, false, 2>(ctx, a, ctas_per_sm, st);
-    default:
-      return dist ? launch_tma<512, 2, true, 1>(ctx, a, ctas_per_sm, st)
-                  : launch_tma<512, 2, false, 1>(ctx, a, ctas_per_sm, st);
+  const bool starts = a.in_starts != nullptr;
+  if (a.bits > 8) {  // 512 bins: 1024-thread tiles of 8192 pairs
+    if (dist) return launch_tma<1024, 1, true, false>(ctx, a, ctas_per_sm, st);
+    return starts ? launch_tma<1024, 1, false, true>(ctx, a, ctas_per_sm, st)
+                  : launch_tma<1024, 1, false, false>(ctx, a, ctas_per_sm, st);
   }
+  if (dist) return launch_tma<512, 2, true, false>(ctx, a, ctas_per_sm, st);
+  return starts ? launch_tma<512, 2, false, true>(ctx, a, ctas_per_sm, st)
+                : launch_tma<512, 2, false, false>(ctx, a, ctas_per_sm, st);
 }
 
 }  // namespace
@@ -752,12 +682,15 @@ int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32
 }
 
 // ---- launch helpers of the multi-GPU join (dist_join.cu) --------------------------------
-// Level 1 of the job on this rank's rows: regions are spread over the GPUs (peer pointers).
-// d_cursors: [2^bits cursors][flag][tile counter], zeroed by the caller.  The rank's counts are
-// handed to the owners of the regions even when it has no rows (they must not see old ones).
+// Level 1 of the job on rows [0, n) of keys_in (a part of this rank's relation): regions are
+// spread over the GPUs (peer pointers).  d_cursors: the rank's 2^bits cursors, which run on over
+// the parts of a relation (zeroed by the caller before the first).  The cursors reached after this
+// part are handed to the owners' count table `count_table` even when the rank has no rows (they
+// must not see old counts).
 int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_in, size_t n,
                             uint32_t iota_base, int shift, int bits, uint32_t out_cap,
                             const hmj_peer_regions& peers, uint32_t* d_cursors, uint32_t* d_flag,
+                            uint32_t* d_tile_counter, uint32_t count_table_offset,
                             uint32_t ctas_per_sm) {
   HMJ_ARG(ctx, (reinterpret_cast<uintptr_t>(keys_in) & 15) == 0 && bits <= 9);
   if (n) {
@@ -768,27 +701,31 @@ int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_
     a.total_tiles = (uint32_t)hmj_div_up(n, tile_items_for(bits));
     a.tiles_per_region = a.total_tiles;
     a.shift = shift; a.bits = bits; a.out_cap = out_cap;
-    a.cursors = d_cursors; a.flag = d_flag; a.tile_counter = d_flag + 1;
+    a.cursors = d_cursors; a.flag = d_flag; a.tile_counter = d_tile_counter;
     a.peers = &peers;
     HMJ_TRY(launch_scatter(ctx, a, ctas_per_sm, st));
     hmj_prof_end_on(ctx, ev, st);
   }
-  push_counts_kernel<<<((1u << bits) + 255) / 256, 256, 0, st>>>(d_cursors, 1u << bits, peers);
+  push_counts_kernel<<<((1u << bits) + 255) / 256, 256, 0, st>>>(d_cursors, 1u << bits, peers,
+                                                                 count_table_offset);
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 
-// A local level on this rank's own regions (`regions` of `cap1` slots, counts in cur1) -> padded
-// buckets (bucket = ((region >> region_shift) << bits) | digit).
+// A local level on this rank's own regions (`regions` of `cap1` slots holding the pairs
+// [start1[r], cur1[r]); start1 == nullptr: from 0) -> padded buckets
+// (bucket = ((region >> region_shift) << bits) | digit), appended at the buckets' cursors cur2.
 int hmj_scatter_level2(hmj_ctx* ctx, cudaStream_t st, const uint64_t* k1, const uint32_t* v1,
-                       const uint32_t* cur1, uint32_t cap1, uint32_t regions, size_t n_hint, int shift,
-                       int bits, uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag, uint32_t* d_tile_counter, int region_shift) {
+                       const uint32_t* cur1, const uint32_t* start1, uint32_t cap1, uint32_t regions,
+                       size_t n_hint, int shift, int bits, uint64_t* k2, uint32_t* v2,
+                       uint32_t cap_seg, uint32_t* cur2, uint32_t* d_flag, uint32_t* d_tile_counter,
+                       int region_shift) {
   cudaEvent_t ev;
   HMJ_TRY(hmj_prof_begin_on(ctx, HMJ_K_SCATTER, (double)n_hint * 24.0, &ev, st));
   ScatterLaunch a = {};
-  a.keys_in = k1; a.vals_in = v1; a.in_counts = cur1; a.in_stride = cap1;
-  a.tiles_per_region = (uint32_t)hmj_div_up(cap1, tile_items_for(bits));
+  a.keys_in = k1; a.vals_in = v1; a.in_counts = cur1; a.in_starts = start1; a.in_stride = cap1;
+  // (+1 tile: a part may start up to 3 pairs before a tile boundary of the region)
+  a.tiles_per_region = (uint32_t)hmj_div_up(cap1, tile_items_for(bits)) + (start1 ? 1u : 0u);
   a.total_tiles = regions * a.tiles_per_region;
   a.keys_out = k2; a.vals_out = v2;
   a.shift = shift; a.bits = bits; a.out_cap = cap_seg;

@@ -198,11 +198,13 @@ struct hmj_peer_regions {
 int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_in, size_t n,
                             uint32_t iota_base, int shift, int bits, uint32_t out_cap,
                             const hmj_peer_regions& peers, uint32_t* d_cursors, uint32_t* d_flag,
+                            uint32_t* d_tile_counter, uint32_t count_table_offset,
                             uint32_t ctas_per_sm);
 int hmj_scatter_level2(hmj_ctx* ctx, cudaStream_t st, const uint64_t* k1, const uint32_t* v1,
-                       const uint32_t* cur1, uint32_t cap1, uint32_t regions, size_t n_hint, int shift,
-                       int bits, uint64_t* k2, uint32_t* v2, uint32_t cap_seg, uint32_t* cur2,
-                       uint32_t* d_flag, uint32_t* d_tile_counter, int region_shift);
+                       const uint32_t* cur1, const uint32_t* start1, uint32_t cap1, uint32_t regions,
+                       size_t n_hint, int shift, int bits, uint64_t* k2, uint32_t* v2,
+                       uint32_t cap_seg, uint32_t* cur2, uint32_t* d_flag, uint32_t* d_tile_counter,
+                       int region_shift);
 struct hmj_uniform_plan {
   int levels;        // 0 = not eligible
   int bits[2];

@@ -13,26 +13,31 @@
 // shared partitions (partitioned_hash.h:82-124) at the scale of a node.
 //
 // One join is ONE call (hmj_dist_join_u64) that only enqueues work; the GPUs meet through flags in
-// each other's memory, not through host barriers:
-//   main stream  wait DONE(R, last join) -> level 1 of R over NVLink -> counts -> READY(R) to all
-//                wait DONE(S, last join) -> level 1 of S over NVLink -> counts -> READY(S) to all
-//                [after the side stream] wait READY(S) from all -> local levels of S -> DONE(S) to all
-//                -> bucket join
-//   side stream  wait READY(R) from all -> local levels of R -> DONE(R) to all
-// so the local levels of R (HBM-bound) run while S is still crossing NVLink.  READY(side) from
-// source s = "my runs and counts of this join are in your memory" (release store after the
-// kernels that wrote them; the owner acquires it in a one-CTA wait kernel in front of its local
-// level).  DONE(side) from owner o = "I have read your runs of this join": the source's next
-// level 1 waits for it before it overwrites them.  A wait gives up after HMJ_DIST_TIMEOUT_MS
-// (default 20000) and fails the join instead of hanging the GPU.
-// Level 1 of S is launched with one CTA per SM and the scatter kernels take their tiles from a
-// counter, so the local levels of R fill the other half of every SM while S is in flight and
-// all of it afterwards.
+// each other's memory, not through host barriers.  Each relation crosses NVLink in PARTS (2 by
+// default, HMJ_DIST_PARTS), so that the owners always have a part to cut locally while the next
+// one is in flight:
+//   exchange stream  [wait DONE(R, last join)] level 1 of R part 0 over NVLink -> counts -> READY(R,0)
+//                    level 1 of R part 1 -> counts -> READY(R,1); the same for S
+//   main stream      wait READY(R,0) from all -> local levels of what R part 0 brought -> ... R part 1
+//                    -> DONE(R) to all -> S part 0 -> S part 1 -> DONE(S) to all -> bucket join
+// A part appends to the same sub-regions (the source's cursors run on); the owner keeps one count
+// table per part, so its local level of part p reads [count(p-1), count(p)) of every sub-region
+// and appends to the final buckets.  READY(side, part) from source s = "my runs and counts of this
+// part are in your memory" (release store after the kernels that wrote them; the owner acquires
+// it in a one-CTA wait kernel in front of its local level).  DONE(side) from owner o = "I have
+// read your runs of this join": the source's next level 1 of that side waits for it before it
+// overwrites them.  A wait gives up after HMJ_DIST_TIMEOUT_MS (default 20000) and fails the join
+// instead of hanging the GPU.
+// All level-1 launches but the first run with one CTA per SM and the scatter kernels take their
+// tiles from a counter, so the local levels fill the other half of every SM while a part is in
+// flight and all of it afterwards.
 //
 // One process per GPU: the regions are cudaMalloc'ed here and shared with CUDA IPC handles that
 // the caller exchanges over torch.distributed (hashmergejoin_b200/dist.py).
 #include <math.h>
 #include <stdlib.h>
+
+#include <algorithm>
 
 #include "common.cuh"
 
@@ -40,10 +45,11 @@ namespace {
 constexpr int HANDLE_BYTES = 64;  // sizeof(cudaIpcMemHandle_t)
 static_assert(sizeof(cudaIpcMemHandle_t) == HANDLE_BYTES, "IPC handle size");
 constexpr int HANDLES_PER_RANK = 7;  // per side: keys, row ids, counts; then the signal words
-enum { SIG_READY = 0, SIG_DONE = 1 };
-// signal words of a rank: [kind][side][source or owner rank], 8 ranks at most
-__host__ __device__ inline int sig_slot(int kind, int side, int rank) { return (kind * 2 + side) * 8 + rank; }
-constexpr int SIG_WORDS = 64;
+constexpr int MAX_PARTS = 4;
+// signal words of a rank, 8 ranks at most: READY [side][part][source rank], DONE [side][owner rank]
+inline int sig_ready(int side, int part, int rank) { return (side * MAX_PARTS + part) * 8 + rank; }
+inline int sig_done(int side, int rank) { return 2 * MAX_PARTS * 8 + side * 8 + rank; }
+constexpr int SIG_WORDS = 2 * MAX_PARTS * 8 + 16;
 
 struct sig_ptrs {
   uint32_t* p[8];
@@ -84,13 +90,15 @@ struct hmj_dist_state {
   // level-1 bits (job wide: the GPU bits + own_bits), local level bits (b3 = 0: one local level)
   int g_bits = 0, b1 = 0, b2 = 0, b3 = 0, own_bits = 0;
   uint32_t cap1 = 0, cap2 = 0, cap_seg = 0, regions_own = 0;
+  int parts = 2;          // parts a relation crosses NVLink in
+  uint32_t ctab = 0;      // words per count table (one table per part)
   // own level-1 regions per side (0 = R, 1 = S): regions_own x world sub-regions of cap1 slots
   // (keys, row ids) and their counts [regions_own * world], all shared with the peers;
   uint64_t* k1[2] = {nullptr, nullptr};
   uint32_t* v1[2] = {nullptr, nullptr};
   uint32_t* c1[2] = {nullptr, nullptr};
   // private: this source's cursors over all 2^b1 regions of the job (+ 8 words: [2^b1] = flag,
-  // [2^b1 + 1] = tile counter of level 1)
+  // [2^b1 + 1 + p] = tile counter of level 1 of part p)
   uint32_t* cur[2] = {nullptr, nullptr};
   uint32_t* sig = nullptr;  // this rank's signal words (shared with the peers)
   sig_ptrs sigs = {};
@@ -98,8 +106,8 @@ struct hmj_dist_state {
   void* opened[8][HANDLES_PER_RANK] = {};
   size_t rows_total = 0;
   uint32_t epoch = 0;
-  cudaStream_t side_stream = nullptr;
-  cudaEvent_t ev_r_sent = nullptr, ev_r_local = nullptr;
+  cudaStream_t side_stream = nullptr;  // the exchange stream
+  cudaEvent_t ev_r_sent = nullptr, ev_r_local = nullptr;  // ev_r_sent: fork main -> exchange
   unsigned long long timeout_ns = 20000ull * 1000000ull;
   // what the last join moved (read back from the cursors and the owners' count tables)
   uint64_t sent_pairs = 0, received_pairs[2] = {0, 0};
@@ -139,6 +147,10 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
     const int v = atoi(e);
     if (v > d->b1 && v <= 9 && v <= total_bits - 1) d->b1 = v;
   }
+  if (const char* e = getenv("HMJ_DIST_PARTS")) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= MAX_PARTS) d->parts = v;
+  }
   if (const char* e = getenv("HMJ_DIST_TIMEOUT_MS")) {
     const long v = atol(e);
     if (v > 0) d->timeout_ns = (unsigned long long)v * 1000000ull;
@@ -174,8 +186,9 @@ extern "C" int hmj_dist_setup(hmj_ctx* ctx, int rank, int world, size_t rows_tot
     const size_t slots = subs * d->cap1;
     HMJ_CUDA(ctx, cudaMalloc(&d->k1[s], slots * 8));
     HMJ_CUDA(ctx, cudaMalloc(&d->v1[s], slots * 4));
-    HMJ_CUDA(ctx, cudaMalloc(&d->c1[s], (subs + 8) * 4));
-    HMJ_CUDA(ctx, cudaMemset(d->c1[s], 0, (subs + 8) * 4));
+    d->ctab = (uint32_t)((subs + 7) & ~size_t(7));
+    HMJ_CUDA(ctx, cudaMalloc(&d->c1[s], (size_t)MAX_PARTS * d->ctab * 4));
+    HMJ_CUDA(ctx, cudaMemset(d->c1[s], 0, (size_t)MAX_PARTS * d->ctab * 4));
     HMJ_CUDA(ctx, cudaMalloc(&d->cur[s], (((size_t)1 << d->b1) + 8) * 4));
     void* ptrs[3] = {d->k1[s], d->v1[s], d->c1[s]};
     for (int j = 0; j < 3; ++j) {
@@ -234,53 +247,55 @@ extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) 
 
 namespace {
 
-int dist_signal(hmj_ctx* ctx, cudaStream_t st, int kind, int side) {
+int dist_signal(hmj_ctx* ctx, cudaStream_t st, int slot) {
   hmj_dist_state* d = ctx->dist;
-  dist_signal_kernel<<<1, 32, 0, st>>>(d->sigs, d->world, sig_slot(kind, side, d->rank), d->epoch);
+  dist_signal_kernel<<<1, 32, 0, st>>>(d->sigs, d->world, slot, d->epoch);
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 
-int dist_wait(hmj_ctx* ctx, cudaStream_t st, int kind, int side, uint32_t epoch) {
+// all `world` words from d->sig + slot0 on must reach `epoch`
+int dist_wait(hmj_ctx* ctx, cudaStream_t st, int slot0, int side, uint32_t epoch) {
   hmj_dist_state* d = ctx->dist;
   uint32_t* fail = d->cur[side] + ((size_t)1 << d->b1);
-  dist_wait_kernel<<<1, 32, 0, st>>>(d->sig + sig_slot(kind, side, 0), d->world, epoch, fail,
-                                     d->timeout_ns);
+  dist_wait_kernel<<<1, 32, 0, st>>>(d->sig + slot0, d->world, epoch, fail, d->timeout_ns);
   HMJ_LAUNCHED(ctx);
   return HMJ_OK;
 }
 
-// local levels of `side` on this rank's hash range -> padded final buckets
-int dist_local_levels(hmj_ctx* ctx, cudaStream_t st, int s, hmj_uniform_buckets* out) {
+// local levels of what part `part` of `side` brought into this rank's sub-regions -> appended to
+// the padded final buckets.  words: [8 tile counters][final cursors: buckets][middle: regions2]
+int dist_local_levels(hmj_ctx* ctx, cudaStream_t st, int s, int part, hmj_uniform_buckets* out) {
   hmj_dist_state* d = ctx->dist;
   const uint32_t regions2 = d->regions_own << d->b2;  // after the first local level
   const uint32_t buckets = regions2 << d->b3;         // final
-  const size_t n_hint = d->rows_total / d->world;
-  // scratch words: [8: tile counters at 1, 2][final cursors: buckets][middle cursors: regions2]
+  const size_t n_hint = d->rows_total / d->world / d->parts;
   uint32_t* words = reinterpret_cast<uint32_t*>(ctx->ws[s ? WS_US_CURSORS_1 : WS_US_CURSORS].ptr);
-  const size_t nwords = (size_t)8 + buckets + (d->b3 ? regions2 : 0);
-  HMJ_TRY(hmj_fill_async(ctx, words, 0, nwords * 4, st));
   uint64_t* k2 = reinterpret_cast<uint64_t*>(ctx->ws[s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B].ptr);
   uint32_t* v2 = reinterpret_cast<uint32_t*>(ctx->ws[s ? WS_SORT_VALS_C : WS_SORT_VALS_B].ptr);
   uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);  // this rank's level-1 overflows land here too
   const uint32_t subs = d->regions_own * (uint32_t)d->world;
+  const uint32_t* ends = d->c1[s] + (size_t)part * d->ctab;
+  const uint32_t* starts = part ? d->c1[s] + (size_t)(part - 1) * d->ctab : nullptr;
+  const bool last = part == d->parts - 1;
   if (d->b3 == 0) {
-    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
+    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], ends, starts, d->cap1, subs, n_hint,
                                64 - d->b1 - d->b2, d->b2, k2, v2, d->cap_seg, words + 8, flag,
-                               words + 1, d->g_bits));
-    HMJ_TRY(dist_signal(ctx, st, SIG_DONE, s));
+                               words + 2 * part, d->g_bits));
+    if (last) HMJ_TRY(dist_signal(ctx, st, sig_done(s, d->rank)));
   } else {
-    // sub-regions -> regions2 middle regions (one buffer, used by R then by S) -> final buckets
+    // sub-regions -> regions2 middle regions (one buffer, refilled by every part) -> final buckets
     uint64_t* km = reinterpret_cast<uint64_t*>(ctx->ws[WS_SORT_KEYS_A].ptr);
     uint32_t* vm = reinterpret_cast<uint32_t*>(ctx->ws[WS_SORT_VALS_A].ptr);
     uint32_t* cur_mid = words + 8 + buckets;
-    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], d->c1[s], d->cap1, subs, n_hint,
-                               64 - d->b1 - d->b2, d->b2, km, vm, d->cap2, cur_mid, flag, words + 1,
-                               d->g_bits));
-    HMJ_TRY(dist_signal(ctx, st, SIG_DONE, s));
-    HMJ_TRY(hmj_scatter_level2(ctx, st, km, vm, cur_mid, d->cap2, regions2, n_hint,
+    HMJ_TRY(hmj_fill_async(ctx, cur_mid, 0, (size_t)regions2 * 4, st));
+    HMJ_TRY(hmj_scatter_level2(ctx, st, d->k1[s], d->v1[s], ends, starts, d->cap1, subs, n_hint,
+                               64 - d->b1 - d->b2, d->b2, km, vm, d->cap2, cur_mid, flag,
+                               words + 2 * part, d->g_bits));
+    if (last) HMJ_TRY(dist_signal(ctx, st, sig_done(s, d->rank)));
+    HMJ_TRY(hmj_scatter_level2(ctx, st, km, vm, cur_mid, nullptr, d->cap2, regions2, n_hint,
                                64 - d->b1 - d->b2 - d->b3, d->b3, k2, v2, d->cap_seg, words + 8, flag,
-                               words + 2, 0));
+                               words + 2 * part + 1, 0));
   }
   out->keys = k2;
   out->vals = v2;
@@ -308,7 +323,7 @@ extern "C" int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t n
   hmj_dist_state* d = ctx->dist;
   HMJ_ARG(ctx, d->sigs.p[d->rank] != nullptr);  // hmj_dist_connect has run
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream, st2 = d->side_stream;
+  cudaStream_t st = ctx->stream, sx = d->side_stream;
   *ok = 0;
   *h_num_pairs = 0;
   ctx->tm.sort_passes = ctx->tm.sort_finishes = ctx->tm.sort_fallbacks = ctx->tm.sort_uniform = 0;
@@ -317,10 +332,10 @@ extern "C" int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t n
 
   // every buffer of the join, before anything is enqueued (growing one synchronises the stream)
   const uint32_t regions2 = d->regions_own << d->b2, buckets = regions2 << d->b3;
+  const size_t nwords = (size_t)8 + buckets + (d->b3 ? regions2 : 0);
   for (int s = 0; s < 2; ++s) {
     void* p = nullptr;
-    HMJ_TRY(hmj_ws_get(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS,
-                       ((size_t)8 + buckets + (d->b3 ? regions2 : 0)) * 4, &p));
+    HMJ_TRY(hmj_ws_get(ctx, s ? WS_US_CURSORS_1 : WS_US_CURSORS, nwords * 4, &p));
     HMJ_TRY(hmj_ws_get(ctx, s ? WS_SORT_KEYS_C : WS_SORT_KEYS_B, (size_t)buckets * d->cap_seg * 8, &p));
     HMJ_TRY(hmj_ws_get(ctx, s ? WS_SORT_VALS_C : WS_SORT_VALS_B, (size_t)buckets * d->cap_seg * 4, &p));
   }
@@ -335,30 +350,40 @@ extern "C" int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t n
   enum { EV_START = 0, EV_HASHED, EV_SORTED, EV_JOINED };
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_START], st));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_HASHED], st));  // identity hash: no kernel
-  for (int s = 0; s < 2; ++s) HMJ_TRY(hmj_fill_async(ctx, d->cur[s], 0, cur_words * 4, st));
-
-  // R crosses NVLink
-  HMJ_TRY(dist_wait(ctx, st, SIG_DONE, 0, epoch - 1));
-  HMJ_TRY(hmj_scatter_level1_dist(ctx, st, d_rkeys, nr, r_rowid_base, 64 - d->b1, d->b1, d->cap1,
-                                  d->peers[0], d->cur[0], d->cur[0] + ((size_t)1 << d->b1), 0));
-  HMJ_TRY(dist_signal(ctx, st, SIG_READY, 0));
+  for (int s = 0; s < 2; ++s) {
+    HMJ_TRY(hmj_fill_async(ctx, d->cur[s], 0, cur_words * 4, st));
+    HMJ_TRY(hmj_fill_async(ctx, ctx->ws[s ? WS_US_CURSORS_1 : WS_US_CURSORS].ptr, 0, nwords * 4, st));
+  }
   HMJ_CUDA(ctx, cudaEventRecord(d->ev_r_sent, st));
-  // side stream: R's local levels as soon as every source's runs are here
-  hmj_uniform_buckets B[2];
-  HMJ_CUDA(ctx, cudaStreamWaitEvent(st2, d->ev_r_sent, 0));
-  HMJ_TRY(dist_wait(ctx, st2, SIG_READY, 0, epoch));
-  HMJ_TRY(dist_local_levels(ctx, st2, 0, &B[0]));
-  HMJ_CUDA(ctx, cudaEventRecord(d->ev_r_local, st2));
-  // S crosses NVLink meanwhile (one CTA per SM: the other half of every SM is R's)
-  HMJ_TRY(dist_wait(ctx, st, SIG_DONE, 1, epoch - 1));
+  HMJ_CUDA(ctx, cudaStreamWaitEvent(sx, d->ev_r_sent, 0));
+
+  // exchange stream: both relations, part by part, over NVLink
   const char* e1 = getenv("HMJ_DIST_S_CTAS");
-  HMJ_TRY(hmj_scatter_level1_dist(ctx, st, d_skeys, ns, s_rowid_base, 64 - d->b1, d->b1, d->cap1,
-                                  d->peers[1], d->cur[1], d->cur[1] + ((size_t)1 << d->b1),
-                                  e1 ? (uint32_t)atoi(e1) : 1u));
-  HMJ_TRY(dist_signal(ctx, st, SIG_READY, 1));
-  HMJ_CUDA(ctx, cudaStreamWaitEvent(st, d->ev_r_local, 0));
-  HMJ_TRY(dist_wait(ctx, st, SIG_READY, 1, epoch));
-  HMJ_TRY(dist_local_levels(ctx, st, 1, &B[1]));
+  const uint32_t later_ctas = e1 ? (uint32_t)atoi(e1) : 1u;
+  for (int s = 0; s < 2; ++s) {
+    const uint64_t* keys = s ? d_skeys : d_rkeys;
+    const size_t n = s ? ns : nr;
+    const uint32_t base = s ? s_rowid_base : r_rowid_base;
+    uint32_t* flag = d->cur[s] + ((size_t)1 << d->b1);
+    // part boundaries on multiples of 4096 rows: tiles stay 16-byte aligned
+    const size_t per = ((n / d->parts + 4095) & ~size_t(4095));
+    HMJ_TRY(dist_wait(ctx, sx, sig_done(s, 0), s, epoch - 1));
+    for (int part = 0; part < d->parts; ++part) {
+      const size_t lo = std::min(n, per * part);
+      const size_t hi = part == d->parts - 1 ? n : std::min(n, per * (part + 1));
+      HMJ_TRY(hmj_scatter_level1_dist(ctx, sx, keys + lo, hi - lo, base + (uint32_t)lo, 64 - d->b1, d->b1,
+                                      d->cap1, d->peers[s], d->cur[s], flag, flag + 1 + part,
+                                      (uint32_t)part * d->ctab, (s == 0 && part == 0) ? 0u : later_ctas));
+      HMJ_TRY(dist_signal(ctx, sx, sig_ready(s, part, d->rank)));
+    }
+  }
+  // main stream: the local levels of every part as it arrives, then the join
+  hmj_uniform_buckets B[2];
+  for (int s = 0; s < 2; ++s)
+    for (int part = 0; part < d->parts; ++part) {
+      HMJ_TRY(dist_wait(ctx, st, sig_ready(s, part, 0), s, epoch));
+      HMJ_TRY(dist_local_levels(ctx, st, s, part, &B[s]));
+    }
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_SORTED], st));
 
   const size_t n_hint = d->rows_total / d->world;
@@ -366,6 +391,7 @@ extern "C" int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t n
                               64 - d->b1 - d->b2 - d->b3 - 12, n_hint, n_hint, nullptr, nullptr,
                               nullptr, nullptr, h_num_pairs, ok));
   HMJ_CUDA(ctx, cudaEventRecord(ctx->ev[EV_JOINED], st));
+  HMJ_CUDA(ctx, cudaStreamSynchronize(sx));
   if (*ok) ctx->tm.bucket_join = 1;
   return HMJ_OK;
 }
@@ -387,7 +413,7 @@ extern "C" int hmj_dist_last_exchange(hmj_ctx* ctx, uint64_t* sent_pairs_remote,
     HMJ_CUDA(ctx, cudaMemcpy(h.data(), d->cur[s], regions * 4, cudaMemcpyDeviceToHost));
     for (size_t r = 0; r < regions; ++r)
       if ((int)(r >> d->own_bits) != d->rank) sent += h[r];
-    HMJ_CUDA(ctx, cudaMemcpy(h.data(), d->c1[s], subs * 4, cudaMemcpyDeviceToHost));
+    HMJ_CUDA(ctx, cudaMemcpy(h.data(), d->c1[s] + (size_t)(d->parts - 1) * d->ctab, subs * 4, cudaMemcpyDeviceToHost));
     for (size_t r = 0; r < subs; ++r) recv[s] += h[r];
   }
   if (sent_pairs_remote) *sent_pairs_remote = sent;

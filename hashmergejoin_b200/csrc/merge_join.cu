@@ -64,6 +64,13 @@ struct JoinArgs {
   uint32_t* tile_counter;      // dynamic tile ids (fused mode)
   uint64_t cap;                // capacity of out_r/out_s in pairs (fused mode)
   uint32_t tiles;
+  // Fused mode, string keys: count every hash-equal candidate as a match and verify the keys only
+  // once, where the pair is written (a candidate's key bytes are a random gather; verifying in the
+  // count phase AND in the write phase made the join of C5 gather every probe key twice).  A
+  // candidate that fails the key check -- two different keys with one 64-bit hash -- raises
+  // *collision and the host re-runs the exact two-phase join.
+  int optimistic;
+  uint32_t* collision;
 };
 
 // first index in [lo,hi) of sorted a[] with a[idx] >= v   (hi if none)
@@ -177,7 +184,9 @@ struct JoinShared {  // lives behind the tile arrays in dynamic shared memory
 template <int KIND>
 __device__ __forceinline__ bool cand_ok(const JoinArgs& A, uint32_t rrow, uint32_t srow) {
   if (KIND == HMJ_KEY_U64) return true;
-  return keys_equal_str(A.roff, A.rchars, rrow, A.soff, A.schars, srow);
+  const bool ok = keys_equal_str(A.roff, A.rchars, rrow, A.soff, A.schars, srow);
+  if (!ok && A.optimistic) *reinterpret_cast<volatile uint32_t*>(A.collision) = 1u;
+  return ok;
 }
 
 // all threads: verified candidates of every queued run -> p_res[owner]
@@ -390,7 +399,7 @@ join_tile_kernel(const JoinArgs A) {
       const uint32_t ub = (u == nb) ? gallop_upper(A.sh, b1, A.ns, h) : b0 + u;
       ncand = ub - lb;
       if (NEED_IDS) rrow = A.rr[a0 + li];
-      if (KIND == HMJ_KEY_U64) {
+      if (KIND == HMJ_KEY_U64 || (MODE == JOIN_FUSED && A.optimistic)) {
         cnt = ncand;
       } else if (ncand > (uint32_t)JOIN_BIG) {
         big = true;
@@ -702,11 +711,23 @@ int join_fused(hmj_ctx* ctx, JoinPlan* plan, uint32_t* d_out_r, uint32_t* d_out_
   A.out_r = d_out_r;
   A.out_s = d_out_s;
   A.cap = cap;
-  HMJ_TRY(hmj_fill_async(ctx, A.tile_desc, 0, (size_t)A.tiles * 8 + 16, ctx->stream));
-  HMJ_TRY(launch_tiles<JOIN_FUSED>(ctx, *plan));
+  static const bool allow_optimistic = [] {
+    const char* e = getenv("HMJ_JOIN_OPTIMISTIC");
+    return !(e && atoi(e) == 0);
+  }();
   uint64_t* h = reinterpret_cast<uint64_t*>(ctx->pinned);
-  HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.agg + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
-  HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  A.collision = A.tile_counter + 2;  // inside the zeroed tail of the descriptors
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    A.optimistic = (attempt == 0 && allow_optimistic && plan->kind == HMJ_KEY_STRING) ? 1 : 0;
+    HMJ_TRY(hmj_fill_async(ctx, A.tile_desc, 0, (size_t)A.tiles * 8 + 16, ctx->stream));
+    HMJ_TRY(launch_tiles<JOIN_FUSED>(ctx, *plan));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h, A.agg + 2, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HMJ_CUDA(ctx, cudaMemcpyAsync(h + 1, A.collision, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    HMJ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!A.optimistic || (uint32_t)h[1] == 0) break;
+    // two different keys under one hash: the optimistic counts were too high, join again exactly
+  }
+  A.optimistic = 0;
   *h_total = h[0];
   if (ctx->prof_on && ctx->prof_used >= 2 && h[0] <= cap)
     ctx->prof_bytes[ctx->prof_used / 2 - 1] += 8.0 * (double)h[0];
