@@ -810,6 +810,10 @@ def run_gpu_strings(args, wl):
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "verified": verified,
         }
+        if joiner is not None and joiner.trace:
+            log("string exchange phases (rank 0, ms, device-synchronised):")
+            for what, ms in joiner.trace_log[-30:]:
+                log("   %-36s %8.2f" % (what, ms))
         if joiner is not None:
             line["nvlink"] = {"bytes_sent_to_peers_rank0_per_join": joiner.exchange_bytes,
                               "rows_received_rank0": list(joiner.local_rows),

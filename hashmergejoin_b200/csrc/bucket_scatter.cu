@@ -341,7 +341,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
-      if (i >= lo && i < valid) {
+      if ((!STARTS || i >= lo) && i < valid) {
         key[k] = b_keys[i];
         slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
         if (prefix_bits) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
@@ -361,7 +361,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
-      if (i >= lo && i < valid) val[k] = vals_in ? b_vals[i] : in_base + i + iota_base;
+      if ((!STARTS || i >= lo) && i < valid) val[k] = vals_in ? b_vals[i] : in_base + i + iota_base;
     }
     {
       uint32_t x = c;
@@ -382,7 +382,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
       const uint32_t i = tid + k * UT_THREADS;
-      if (i >= lo && i < valid) {
+      if ((!STARTS || i >= lo) && i < valid) {
         const uint32_t p = s_off[(uint32_t)(key[k] >> shift) & mask] + slot[k];
         b_keys[p] = key[k];
         b_vals[p] = val[k];

@@ -90,7 +90,7 @@ struct hmj_dist_state {
   // level-1 bits (job wide: the GPU bits + own_bits), local level bits (b3 = 0: one local level)
   int g_bits = 0, b1 = 0, b2 = 0, b3 = 0, own_bits = 0;
   uint32_t cap1 = 0, cap2 = 0, cap_seg = 0, regions_own = 0;
-  int parts = 2;          // parts a relation crosses NVLink in
+  int parts = 1;          // parts a relation crosses NVLink in (HMJ_DIST_PARTS)
   uint32_t ctab = 0;      // words per count table (one table per part)
   // own level-1 regions per side (0 = R, 1 = S): regions_own x world sub-regions of cap1 slots
   // (keys, row ids) and their counts [regions_own * world], all shared with the peers;

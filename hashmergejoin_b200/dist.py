@@ -52,7 +52,7 @@ def exchange_pairs(part_hash, part_rowid, part_offsets, rank, world, group=None)
     return rh, rr, mat
 
 
-def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, world, group=None):
+def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, world, group=None, mark=None):
     """The exchange step for string keys: the keys travel with their rows.
     part_rowid: this rank's global row ids grouped by destination (bucket g at
     [part_offsets[g], part_offsets[g+1])); key_offsets/key_chars: the keys in that same order.
@@ -77,9 +77,15 @@ def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, wor
     r_rowid = torch.empty(sum(recv_rows), dtype=part_rowid.dtype, device=dev)
     r_lens = torch.empty(sum(recv_rows), dtype=torch.int32, device=dev)
     r_chars = torch.empty(sum(recv_bytes), dtype=key_chars.dtype, device=dev)
+    if mark:
+        mark("  counts + planning")
     dist.all_to_all_single(r_rowid, part_rowid.contiguous(), recv_rows, send_rows, group=group)
     dist.all_to_all_single(r_lens, lens, recv_rows, send_rows, group=group)
+    if mark:
+        mark("  all_to_all row ids + lengths")
     dist.all_to_all_single(r_chars, key_chars.contiguous(), recv_bytes, send_bytes, group=group)
+    if mark:
+        mark("  all_to_all key bytes")
     r_off = torch.zeros(r_lens.numel() + 1, dtype=torch.int64, device=dev)
     if r_lens.numel():
         torch.cumsum(r_lens.to(torch.int64), 0, out=r_off[1:])
@@ -103,6 +109,8 @@ class DistJoin:
         self.fused = False
         self.fused_joins = 0
         self.fallback_joins = 0
+        self.trace = os.environ.get("HMJ_DIST_TRACE", "0") != "0"
+        self.trace_log = []
         if world > 1 and rows_total_hint > 0 and dist.get_backend() == "nccl" \
                 and os.environ.get("HMJ_DIST_FUSED", "1") != "0":
             try:
@@ -197,12 +205,31 @@ class DistJoin:
         if G == 1:
             rid = torch.arange(rowid_base, rowid_base + n, dtype=torch.int64, device=offsets.device).to(torch.int32)
             return rid, offsets, chars
+        mark = self._mark
+        mark("start")
         h = ctx.hash_strings(offsets, chars)
+        mark("hash")
         _, rows, offs = ctx.partition_pairs(h, None, self.bits, rowid_base=0)   # local row ids by destination
+        del h
+        mark("partition")
         k_off, k_chars = ctx.gather_strings(offsets, chars, rows)
-        rid, r_off, r_chars, sent = exchange_strings(rows + rowid_base, offs, k_off, k_chars, self.rank, G)
+        mark("gather keys")
+        rid, r_off, r_chars, sent = exchange_strings(rows + rowid_base, offs, k_off, k_chars, self.rank, G,
+                                                     mark=mark)
+        mark("exchange")
         self.exchange_bytes += sent
         return rid, r_off, r_chars
+
+    def _mark(self, what):
+        """HMJ_DIST_TRACE=1: device-synchronised wall-clock marks of the string exchange's phases"""
+        if not self.trace:
+            return
+        import time
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        if what != "start":
+            self.trace_log.append((what, (now - self._t_last) * 1e3))
+        self._t_last = now
 
     def join_strings(self, roff_local, rchars_local, soff_local, schars_local, want_pairs=False):
         """String-key join over the ranks (C5's shape).  Each rank passes its block of both
@@ -216,7 +243,9 @@ class DistJoin:
         s_id, s_off, s_chars = self._exchange_side_strings(soff_local, schars_local, self.rank * ns)
         self.local_rows = (r_id.numel(), s_id.numel())
         # received keys are indexed by arrival position; the join reports positions
+        self._mark("start")
         m = ctx.join_strings(r_off, r_chars, s_off, s_chars, prefix_bits=self.bits)
+        self._mark("local join")
         if not want_pairs:
             return m
         out_r, out_s = ctx.join_result_tensors(m)
