@@ -207,8 +207,9 @@ __device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint3
 // [in_starts[r], in_counts[r]); earlier parts of the region were processed by an earlier launch.
 // The first tile of a region then starts at in_starts[r] rounded down to 4 pairs (bulk copies need
 // 16-byte aligned sources) and ignores the `lo` pairs before the start.
-// STARTS = false compiles the region starts out (every level but the local ones of the multi-GPU join)
-template <int UT_THREADS, int MIN_BLOCKS, bool DIST, bool STARTS>
+// VARIANT compiles the rarely used paths out of the common kernel: 0 plain, 1 region starts (local
+// levels of the multi-GPU join taken in parts), 2 prefix check (first level of a sample-derived plan)
+template <int UT_THREADS, int MIN_BLOCKS, bool DIST, int VARIANT>
 __global__ void __launch_bounds__(UT_THREADS, MIN_BLOCKS)
 bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                           const uint32_t* __restrict__ in_counts, const uint32_t* __restrict__ in_starts,
@@ -219,6 +220,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
                           uint32_t* __restrict__ tile_counter, const hmj_peer_regions peers,
                           int region_shift, uint64_t prefix, int prefix_bits) {
   using Cfg = UtCfg<UT_THREADS>;
+  constexpr bool STARTS = VARIANT == 1, PREFIX = VARIANT == 2;
   constexpr int UT_TILE = Cfg::TILE;
   constexpr size_t UT_BUF_BYTES = Cfg::BUF_BYTES;
   extern __shared__ __align__(128) unsigned char smem_tma[];
@@ -344,7 +346,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       if ((!STARTS || i >= lo) && i < valid) {
         key[k] = b_keys[i];
         slot[k] = (uint16_t)atomicAdd(&s_cnt[(uint32_t)(key[k] >> shift) & mask], 1u);
-        if (prefix_bits) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
+        if (PREFIX) stray |= (key[k] >> (64 - prefix_bits)) != prefix;
       }
     }
     __syncthreads();
@@ -484,11 +486,11 @@ struct ScatterLaunch {
   int prefix_bits;
 };
 
-template <int T, int B, bool DIST, bool STARTS>
+template <int T, int B, bool DIST, int VARIANT>
 int launch_tma(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
   using Cfg = UtCfg<T>;
   static_assert(Cfg::SMEM * B + 1024 * B <= 233472, "scatter configuration does not fit an SM");
-  auto* kern = bucket_scatter_tma_kernel<T, B, DIST, STARTS>;
+  auto* kern = bucket_scatter_tma_kernel<T, B, DIST, VARIANT>;
   HMJ_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
   const uint32_t per_sm = ctas_per_sm == 0 || ctas_per_sm > (uint32_t)B ? (uint32_t)B : ctas_per_sm;
   const uint32_t grid = std::min(a.total_tiles, (uint32_t)ctx->num_sms * per_sm);
@@ -509,15 +511,20 @@ uint32_t tile_items_for(int bits) { return bits > 8 ? 8192u : 4096u; }
 int launch_scatter(hmj_ctx* ctx, const ScatterLaunch& a, uint32_t ctas_per_sm, cudaStream_t st) {
   if (a.total_tiles == 0) return HMJ_OK;
   const bool dist = a.peers != nullptr;
-  const bool starts = a.in_starts != nullptr;
-  if (a.bits > 8) {  // 512 bins: 1024-thread tiles of 8192 pairs
-    if (dist) return launch_tma<1024, 1, true, false>(ctx, a, ctas_per_sm, st);
-    return starts ? launch_tma<1024, 1, false, true>(ctx, a, ctas_per_sm, st)
-                  : launch_tma<1024, 1, false, false>(ctx, a, ctas_per_sm, st);
+  const int variant = a.in_starts != nullptr ? 1 : a.prefix_bits > 0 ? 2 : 0;
+  if (dist) {
+    HMJ_ARG(ctx, variant == 0);
+    return a.bits > 8 ? launch_tma<1024, 1, true, 0>(ctx, a, ctas_per_sm, st)
+                      : launch_tma<512, 2, true, 0>(ctx, a, ctas_per_sm, st);
   }
-  if (dist) return launch_tma<512, 2, true, false>(ctx, a, ctas_per_sm, st);
-  return starts ? launch_tma<512, 2, false, true>(ctx, a, ctas_per_sm, st)
-                : launch_tma<512, 2, false, false>(ctx, a, ctas_per_sm, st);
+  if (a.bits > 8) {  // 512 bins: 1024-thread tiles of 8192 pairs
+    return variant == 1 ? launch_tma<1024, 1, false, 1>(ctx, a, ctas_per_sm, st)
+         : variant == 2 ? launch_tma<1024, 1, false, 2>(ctx, a, ctas_per_sm, st)
+                        : launch_tma<1024, 1, false, 0>(ctx, a, ctas_per_sm, st);
+  }
+  return variant == 1 ? launch_tma<512, 2, false, 1>(ctx, a, ctas_per_sm, st)
+       : variant == 2 ? launch_tma<512, 2, false, 2>(ctx, a, ctas_per_sm, st)
+                      : launch_tma<512, 2, false, 0>(ctx, a, ctas_per_sm, st);
 }
 
 }  // namespace
