@@ -687,7 +687,7 @@ def run_gpu_strings(args, wl):
     if world > 1:
         assert kind != "sort", "c2 is a single-GPU workload"
         from hashmergejoin_b200.dist import DistJoin
-        joiner = DistJoin(ctx, rank, world)
+        joiner = DistJoin(ctx, rank, world, string_rows_hint=rows_total)
     out_h = torch.empty(rows, dtype=torch.int64, device=device) if kind == "sort" else None
     out_v = torch.empty(rows, dtype=torch.int32, device=device) if kind == "sort" else None
     pair_keys = {}
@@ -805,7 +805,7 @@ def run_gpu_strings(args, wl):
                                path_name(tm),
                        "bucket_join": bool(tm["bucket_join"]), "scatter_levels_per_join": tm["scatter_levels"],
                        "sort_passes_per_join": tm["sort_passes"], "sort_fallbacks": tm["sort_fallbacks"],
-                       "parallelism": "hash-range partition x%d%s" % (world, " (NCCL all-to-all of rows + key bytes)" if world > 1 else "")},
+                       "parallelism": "hash-range partition x%d%s" % (world, " (rows + key bytes travel to the owners)" if world > 1 else "")},
             "stage_ms_last_step": {k: tm[k] for k in ("hash_ms", "sort_ms", "join_ms", "total_ms")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "verified": verified,
@@ -816,6 +816,9 @@ def run_gpu_strings(args, wl):
                 log("   %-36s %8.2f" % (what, ms))
         if joiner is not None:
             line["nvlink"] = {"bytes_sent_to_peers_rank0_per_join": joiner.exchange_bytes,
+                              "route": "key gather fused with the exchange: one kernel writes keys, row ids and lengths into the owners' buffers over NVLink"
+                                       if joiner.xchg_joins else "NCCL all_to_all_single x3",
+                              "fused_exchange_joins": joiner.xchg_joins,
                               "rows_received_rank0": list(joiner.local_rows),
                               "note": "row id (4 B) + length (4 B) + key bytes per row leaving the rank; the head key's owner receives more"}
         print_line(line)

@@ -78,6 +78,8 @@ SIGNATURES = {
     "hmj_join_strings": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _U64P]),
     "hmj_join_strings_range": (_I, [_P, _P, _P, _SZ, _P, _P, _SZ, _I, _U64P]),
     "hmj_gather_strings": (_I, [_P, _P, _P, _P, _SZ, _P, _P]),
+    "hmj_string_row_spans": (_I, [_P, _P, _P, _SZ, _P, _P]),
+    "hmj_gather_spans": (_I, [_P, _P, _P, _SZ, _P, _P]),
     "hmj_set_join_order": (_I, [_P, _I]),
     "hmj_join_result": (_I, [_P, C.POINTER(_P), C.POINTER(_P), _U64P]),
     "hmj_join_result_copy": (_I, [_P, _P, _P, _SZ]),
@@ -102,6 +104,12 @@ SIGNATURES = {
     "hmj_dist_join_u64": (_I, [_P, _P, _SZ, C.c_uint32, _P, _SZ, C.c_uint32, _U64P, C.POINTER(C.c_int)]),
     "hmj_dist_last_exchange": (_I, [_P, _U64P, _U64P, _U64P]),
     "hmj_dist_teardown": (_I, [_P]),
+    "hmj_xchg_handle_bytes": (_I, []),
+    "hmj_xchg_setup": (_I, [_P, _I, _I, _SZ, _SZ, _P]),
+    "hmj_xchg_connect": (_I, [_P, _P]),
+    "hmj_xchg_send": (_I, [_P, _I, _P, _P, _P, _P, _P, _SZ, _P, _P, _P]),
+    "hmj_xchg_buffers": (_I, [_P, _I, C.POINTER(_P), C.POINTER(_P), C.POINTER(_P), C.POINTER(_SZ), C.POINTER(_SZ)]),
+    "hmj_xchg_teardown": (_I, [_P]),
     "hmj_gen_permute": (_I, [_P, _P, C.c_uint32, _SZ, C.c_uint32, C.c_uint32, _P]),
     "hmj_gen_zipf": (_I, [_P, _P, C.c_uint32, C.c_uint64, C.c_uint64, _SZ, _P]),
     "hmj_gen_strgen_lengths": (_I, [_P, _P, C.c_uint32, _P, _SZ, _P]),

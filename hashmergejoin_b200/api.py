@@ -24,6 +24,15 @@ def _check_dev(t, dtype_bytes):
         "expected a contiguous CUDA tensor of %d-byte elements" % dtype_bytes
 
 
+class _DeviceSpan:
+    """A raw device allocation of the library seen through __cuda_array_interface__, so that
+    torch.as_tensor can wrap it without a copy."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
 class SortedRelation:
     """Sorted (hash,row-id) columns of one relation plus the key storage the row ids point to."""
 
@@ -226,20 +235,22 @@ class Context:
                                                  prefix_bits, C.byref(m)))
         return m.value
 
-    def gather_strings(self, offsets, chars, rows):
-        """keys of `rows` (int32 tensor of row ids) as a new (offsets, chars) column pair"""
+    def gather_strings(self, offsets, chars, rows, want_lens=False):
+        """keys of `rows` (int32 tensor of row ids) as a new (offsets, chars) column pair; with
+        want_lens also the rows' lengths (int32) in that order"""
         t = self._torch
         _check_dev(offsets, 8)
         n = rows.numel()
-        idx = rows.to(t.int64)
+        start = self._empty(n, t.int64)
+        lens = self._empty(n, t.int32)
+        self._ck(self.lib.hmj_string_row_spans(self.h, _dptr(offsets), _dptr(rows), n, _dptr(start), _dptr(lens)))
         out_off = t.zeros(n + 1, dtype=t.int64, device=offsets.device)
         if n:
-            t.cumsum(offsets[idx + 1] - offsets[idx], 0, out=out_off[1:])
+            t.cumsum(lens, 0, dtype=t.int64, out=out_off[1:])
         total = int(out_off[-1].item()) if n else 0
-        out_chars = self._empty(max(total, 1), t.uint8)[:total]
-        self._ck(self.lib.hmj_gather_strings(self.h, _dptr(offsets), _dptr(chars), _dptr(rows), n,
-                                             _dptr(out_off), _dptr(out_chars)))
-        return out_off, out_chars
+        out_chars = self._empty(total + 16, t.uint8)[:total]
+        self._ck(self.lib.hmj_gather_spans(self.h, _dptr(chars), _dptr(start), n, _dptr(out_off), _dptr(out_chars)))
+        return (out_off, out_chars, lens) if want_lens else (out_off, out_chars)
 
     def join_result_to_host(self, m):
         out_r = np.empty(m, dtype=np.uint32)
@@ -308,6 +319,46 @@ class Context:
         self._ck(self.lib.hmj_hashjoin_build_probe(self.h, C.byref(r), C.byref(s), _dptr(rvals),
                                                    _dptr(svals), C.byref(hits), C.byref(sm)))
         return hits.value, sm.value
+
+    # ---- string keys over several GPUs: key gather fused with the exchange (dist_strings.cu)
+    def string_row_spans(self, offsets, rows):
+        """(start int64, lens int32) of the rows `rows` (int32 tensor) of a string column"""
+        t = self._torch
+        n = rows.numel()
+        start, lens = self._empty(n, t.int64), self._empty(n, t.int32)
+        self._ck(self.lib.hmj_string_row_spans(self.h, _dptr(offsets), _dptr(rows), n, _dptr(start), _dptr(lens)))
+        return start, lens
+
+    def xchg_setup(self, rank, world, rows_cap, bytes_cap):
+        handles = np.zeros(self.lib.hmj_xchg_handle_bytes(), np.uint8)
+        self._ck(self.lib.hmj_xchg_setup(self.h, rank, world, rows_cap, bytes_cap, _hptr(handles)))
+        return handles
+
+    def xchg_connect(self, all_handles):
+        all_handles = np.ascontiguousarray(all_handles, np.uint8)
+        self._ck(self.lib.hmj_xchg_connect(self.h, _hptr(all_handles)))
+
+    def xchg_send(self, side, chars, start, send_off, rowid, lens, part_first, row_base, byte_base):
+        a = [np.ascontiguousarray(x, np.uint64) for x in (part_first, row_base, byte_base)]
+        self._ck(self.lib.hmj_xchg_send(self.h, side, _dptr(chars), _dptr(start), _dptr(send_off), _dptr(rowid),
+                                        _dptr(lens), rowid.numel(), _hptr(a[0]), _hptr(a[1]), _hptr(a[2])))
+
+    def xchg_views(self, side, nrows, nbytes):
+        """(row ids int32[nrows], lengths int32[nrows], key bytes uint8[nbytes]) of this rank's
+        receive buffers, as tensors over the library's memory"""
+        t = self._torch
+        pc, pr, pl = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        rc, bc = C.c_size_t(), C.c_size_t()
+        self._ck(self.lib.hmj_xchg_buffers(self.h, side, C.byref(pc), C.byref(pr), C.byref(pl), C.byref(rc), C.byref(bc)))
+        assert nrows <= rc.value and nbytes <= bc.value
+        def view(ptr, n, typestr, dtype):
+            if n == 0:
+                return t.empty(0, dtype=dtype, device=self.device)
+            return t.as_tensor(_DeviceSpan(ptr.value, n, typestr), device=self.device)
+        return (view(pr, nrows, "<i4", t.int32), view(pl, nrows, "<i4", t.int32), view(pc, nbytes, "|u1", t.uint8))
+
+    def xchg_teardown(self):
+        self._ck(self.lib.hmj_xchg_teardown(self.h))
 
     # ---- device generators of the benchmark relations (datagen.cu)
     def gen_permute(self, n, domain, seed, src=None, base=0):

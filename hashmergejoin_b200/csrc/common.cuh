@@ -82,6 +82,7 @@ struct hmj_ctx {
   std::vector<cudaEvent_t> copy_events;
   // multi-GPU join state (dist_join.cu)
   struct hmj_dist_state* dist = nullptr;
+  struct hmj_xchg_state* xchg = nullptr;  // string-key exchange over peer memory (dist_strings.cu)
   // last whole-operator result
   uint64_t last_pairs = 0;
   hmj_timings tm;

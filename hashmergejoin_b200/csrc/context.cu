@@ -75,10 +75,12 @@ extern "C" int hmj_release_workspace(hmj_ctx* ctx) {
 }
 
 extern "C" int hmj_dist_teardown(hmj_ctx* ctx);
+extern "C" int hmj_xchg_teardown(hmj_ctx* ctx);
 
 extern "C" int hmj_destroy(hmj_ctx* ctx) {
   if (!ctx) return HMJ_EARG;
   hmj_dist_teardown(ctx);
+  hmj_xchg_teardown(ctx);
   hmj_release_workspace(ctx);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);

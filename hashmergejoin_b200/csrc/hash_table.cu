@@ -146,6 +146,9 @@ extern "C" int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r, con
   HMJ_ARG(ctx, r->key_kind == s->key_kind);
   HMJ_ARG(ctx, r->n < (size_t(1) << 32) - 1 && s->n < (size_t(1) << 31));
   HMJ_ARG(ctx, (r->n == 0 || r->d_hash) && (s->n == 0 || s->d_hash));
+  // unsorted relations in row order only: a hash equal to the table's empty marker is told apart
+  // by reading the hash column at the ROW id, which an explicit row-id column would break
+  HMJ_ARG(ctx, r->d_rowid == nullptr && s->d_rowid == nullptr);
   if (r->key_kind == HMJ_KEY_STRING)
     HMJ_ARG(ctx, (r->n == 0 || (r->d_offsets && r->d_chars)) && (s->n == 0 || (s->d_offsets && s->d_chars)));
   HMJ_CUDA(ctx, cudaSetDevice(ctx->device));

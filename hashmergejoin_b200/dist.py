@@ -52,7 +52,8 @@ def exchange_pairs(part_hash, part_rowid, part_offsets, rank, world, group=None)
     return rh, rr, mat
 
 
-def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, world, group=None, mark=None):
+def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, world, group=None, mark=None,
+                     key_lens=None):
     """The exchange step for string keys: the keys travel with their rows.
     part_rowid: this rank's global row ids grouped by destination (bucket g at
     [part_offsets[g], part_offsets[g+1])); key_offsets/key_chars: the keys in that same order.
@@ -73,7 +74,7 @@ def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, wor
     send_bytes, recv_bytes = plan_exchange(byte_mat, rank)
     assert sum(send_rows) == part_rowid.numel() and sum(send_bytes) == key_chars.numel(), \
         "partition offsets do not cover the local rows"
-    lens = (ko[1:] - ko[:-1]).to(torch.int32).contiguous()
+    lens = key_lens if key_lens is not None else (ko[1:] - ko[:-1]).to(torch.int32).contiguous()
     r_rowid = torch.empty(sum(recv_rows), dtype=part_rowid.dtype, device=dev)
     r_lens = torch.empty(sum(recv_rows), dtype=torch.int32, device=dev)
     r_chars = torch.empty(sum(recv_bytes), dtype=key_chars.dtype, device=dev)
@@ -88,7 +89,7 @@ def exchange_strings(part_rowid, part_offsets, key_offsets, key_chars, rank, wor
         mark("  all_to_all key bytes")
     r_off = torch.zeros(r_lens.numel() + 1, dtype=torch.int64, device=dev)
     if r_lens.numel():
-        torch.cumsum(r_lens.to(torch.int64), 0, out=r_off[1:])
+        torch.cumsum(r_lens, 0, dtype=torch.int64, out=r_off[1:])
     sent = 8 * (sum(send_rows) - send_rows[rank]) + sum(send_bytes) - send_bytes[rank]
     return r_rowid, r_off, r_chars, sent
 
@@ -100,7 +101,7 @@ class DistJoin:
     over NVLink, relations pipelined, no host barrier); otherwise, and whenever a region overflows
     (skewed keys), the NCCL path: stable partition pass + all_to_all_single + local join."""
 
-    def __init__(self, ctx, rank, world, rows_total_hint=0):
+    def __init__(self, ctx, rank, world, rows_total_hint=0, string_rows_hint=0, key_bytes_hint=24):
         self.ctx, self.rank, self.world = ctx, rank, world
         self.bits = partition_bits(world)
         self.exchange_bytes = 0      # bytes this rank sent to OTHER ranks in the last join
@@ -111,6 +112,27 @@ class DistJoin:
         self.fallback_joins = 0
         self.trace = os.environ.get("HMJ_DIST_TRACE", "0") != "0"
         self.trace_log = []
+        # string keys: receive buffers in every rank's memory that the peers' gather kernels write
+        # into (hmj_xchg_*); sized from the hint with room for the head key's owner of a Zipf side
+        self.xchg = False
+        self.xchg_joins = 0
+        self.rows_cap = self.bytes_cap = 0
+        if world > 1 and string_rows_hint > 0 and dist.get_backend() == "nccl" \
+                and os.environ.get("HMJ_DIST_FUSED", "1") != "0":
+            self.rows_cap = int(1.6 * string_rows_hint / world) + 4096
+            self.bytes_cap = self.rows_cap * key_bytes_hint
+            try:
+                mine = torch.from_numpy(ctx.xchg_setup(rank, world, self.rows_cap, self.bytes_cap)).cuda()
+                allh = torch.empty(world * mine.numel(), dtype=torch.uint8, device=mine.device)
+                dist.all_gather_into_tensor(allh, mine)
+                ctx.xchg_connect(allh.cpu().numpy())
+                self.xchg = True
+            except Exception as e:
+                self.xchg_error = str(e)
+            flag = torch.tensor([1 if self.xchg else 0], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            self.xchg = bool(flag.item())
+            self._token = torch.zeros(1, dtype=torch.int32, device="cuda")
         if world > 1 and rows_total_hint > 0 and dist.get_backend() == "nccl" \
                 and os.environ.get("HMJ_DIST_FUSED", "1") != "0":
             try:
@@ -127,11 +149,15 @@ class DistJoin:
 
     def close(self):
         """Collective: no rank may free its regions while another still writes into them."""
-        if self.fused:
+        if self.fused or self.xchg:
             torch.cuda.synchronize()
             dist.barrier()
+        if self.fused:
             self.ctx.dist_teardown()
             self.fused = False
+        if self.xchg:
+            self.ctx.xchg_teardown()
+            self.xchg = False
 
     def _exchange_side(self, keys, rowid_base):
         """partition local rows by destination, exchange -> (hash, rowid) tensors of my range"""
@@ -197,9 +223,14 @@ class DistJoin:
         # the rank's hash range shares its top log2(G) bits: bucket join below them
         return ctx.join_pairs(rh, rr, sh, sr, prefix_bits=self.bits)
 
-    def _exchange_side_strings(self, offsets, chars, rowid_base):
-        """hash local keys, group rows by destination, put the keys in send order, exchange ->
-        (global row ids, offsets, chars) of my hash range"""
+    def _rank_barrier(self):
+        """stream-ordered: work enqueued after it runs once every rank's earlier work is done"""
+        dist.all_reduce(self._token)
+
+    def _exchange_side_strings(self, offsets, chars, rowid_base, side=0):
+        """hash local keys, group rows by destination, move row ids + lengths + key bytes to the
+        owners -> (global row ids, offsets, chars) of my hash range.  Returns None for the columns
+        when the fused route was taken (they are read from the receive buffers after the barrier)."""
         ctx, G = self.ctx, self.world
         n = offsets.numel() - 1
         if G == 1:
@@ -212,13 +243,51 @@ class DistJoin:
         _, rows, offs = ctx.partition_pairs(h, None, self.bits, rowid_base=0)   # local row ids by destination
         del h
         mark("partition")
-        k_off, k_chars = ctx.gather_strings(offsets, chars, rows)
-        mark("gather keys")
-        rid, r_off, r_chars, sent = exchange_strings(rows + rowid_base, offs, k_off, k_chars, self.rank, G,
-                                                     mark=mark)
-        mark("exchange")
+        start, lens = ctx.string_row_spans(offsets, rows)
+        k_off = torch.zeros(n + 1, dtype=torch.int64, device=offsets.device)
+        if n:
+            torch.cumsum(lens, 0, dtype=torch.int64, out=k_off[1:])
+        mark("row spans + send offsets")
+        # G x G matrices of rows and key bytes (source-major), the same on every rank
+        po = offs[:G + 1].to(torch.int64)
+        mine = torch.cat([po[1:] - po[:-1], k_off[po[1:]] - k_off[po[:-1]]]).contiguous()
+        allc = torch.empty(G * 2 * G, dtype=torch.int64, device=offsets.device)
+        dist.all_gather_into_tensor(allc, mine)
+        allc = allc.view(G, 2, G).cpu()
+        row_mat, byte_mat = allc[:, 0, :], allc[:, 1, :]
+        recv_rows, recv_bytes = row_mat.sum(0), byte_mat.sum(0)   # per owner
+        mark("counts")
+        rid_send = rows + rowid_base
+        sent = int(8 * (row_mat[self.rank].sum() - row_mat[self.rank][self.rank]) +
+                   byte_mat[self.rank].sum() - byte_mat[self.rank][self.rank])
         self.exchange_bytes += sent
+        if self.xchg and int(recv_rows.max()) <= self.rows_cap and int(recv_bytes.max()) <= self.bytes_cap:
+            part_first = torch.zeros(G + 1, dtype=torch.int64)
+            part_first[1:] = torch.cumsum(row_mat[self.rank], 0)
+            row_base = row_mat[:self.rank].sum(0)      # blocks of the ranks before me, per owner
+            byte_base = byte_mat[:self.rank].sum(0)
+            ctx.xchg_send(side, chars, start, k_off, rid_send, lens, part_first.numpy(), row_base.numpy(),
+                          byte_base.numpy())
+            mark("gather + send over NVLink")
+            return ("fused", int(recv_rows[self.rank]), int(recv_bytes[self.rank]))
+        # NCCL route: keys into send order locally, then three collectives
+        k_chars = ctx._empty(int(k_off[-1].item()) + 16, torch.uint8)[:int(k_off[-1].item())]
+        ctx._ck(ctx.lib.hmj_gather_spans(ctx.h, chars.data_ptr(), start.data_ptr(), n, k_off.data_ptr(),
+                                         k_chars.data_ptr()))
+        mark("gather keys")
+        rid, r_off, r_chars, _ = exchange_strings(rid_send, offs, k_off, k_chars, self.rank, G, mark=mark,
+                                                  key_lens=lens)
+        mark("exchange")
         return rid, r_off, r_chars
+
+    def _received(self, side, got):
+        """columns of a relation that arrived through the receive buffers"""
+        _, nrows, nbytes = got
+        rid, lens, chars = self.ctx.xchg_views(side, nrows, nbytes)
+        off = torch.zeros(nrows + 1, dtype=torch.int64, device=rid.device)
+        if nrows:
+            torch.cumsum(lens, 0, dtype=torch.int64, out=off[1:])
+        return rid, off, chars
 
     def _mark(self, what):
         """HMJ_DIST_TRACE=1: device-synchronised wall-clock marks of the string exchange's phases"""
@@ -239,8 +308,19 @@ class DistJoin:
         ctx = self.ctx
         nr, ns = roff_local.numel() - 1, soff_local.numel() - 1
         self.exchange_bytes = 0
-        r_id, r_off, r_chars = self._exchange_side_strings(roff_local, rchars_local, self.rank * nr)
-        s_id, s_off, s_chars = self._exchange_side_strings(soff_local, schars_local, self.rank * ns)
+        if self.xchg:
+            self._rank_barrier()   # nobody writes into a buffer its owner is still joining from
+        got_r = self._exchange_side_strings(roff_local, rchars_local, self.rank * nr, side=0)
+        got_s = self._exchange_side_strings(soff_local, schars_local, self.rank * ns, side=1)
+        if self.xchg:
+            self._rank_barrier()   # every rank's sends have landed
+            self._mark("start")
+        fused = [isinstance(g[0], str) for g in (got_r, got_s)]
+        r_id, r_off, r_chars = self._received(0, got_r) if fused[0] else got_r
+        s_id, s_off, s_chars = self._received(1, got_s) if fused[1] else got_s
+        if all(fused):
+            self.xchg_joins += 1
+            self._mark("received offsets")
         self.local_rows = (r_id.numel(), s_id.numel())
         # received keys are indexed by arrival position; the join reports positions
         self._mark("start")

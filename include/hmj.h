@@ -161,6 +161,13 @@ int hmj_gather_strings(hmj_ctx* ctx, const uint64_t* d_offsets, const uint8_t* d
  * relations -- the order HashMergeJoin::iterator walks in (hashjoin.h:126-153), identical between
  * runs; the join then always takes the sort + merge-path plan. */
 int hmj_set_join_order(hmj_ctx* ctx, int hash_order);
+/* The same in two steps for callers that also need the rows' lengths (the hash-range exchange
+ * sends them): row_spans reads every row's offset pair once -> start byte and length per row;
+ * after an exclusive prefix sum of the lengths (d_out_offsets), gather_spans copies the bytes. */
+int hmj_string_row_spans(hmj_ctx* ctx, const uint64_t* d_offsets, const uint32_t* d_rows, size_t n,
+                         uint64_t* d_start_out, uint32_t* d_len_out);
+int hmj_gather_spans(hmj_ctx* ctx, const uint8_t* d_chars, const uint64_t* d_start, size_t n,
+                     const uint64_t* d_out_offsets, uint8_t* d_out_chars);
 /* device pointers to the last join's pairs (valid until the next join / destroy). */
 int hmj_join_result(hmj_ctx* ctx, const uint32_t** d_out_r, const uint32_t** d_out_s,
                     uint64_t* num_pairs);
@@ -215,7 +222,8 @@ int hmj_partition_counts_host(hmj_ctx* ctx, const uint64_t* h_hash, size_t n, in
 /* ---- A7: hash-join baseline (build/probe) -------------------------------------------- */
 /* replaces the loops of BM_hash_join_raw (hashjoin_bench.cc:47-53): build an open-addressing
  * table over S (duplicate keys: last row wins, as s_map[k]=v), probe with every R row and
- * return sum += r.value + (hit ? s.value : 0) and the number of hits.  d_*vals NULL = row id. */
+ * return sum += r.value + (hit ? s.value : 0) and the number of hits.  d_*vals NULL = row id.
+ * Both relations in row order (d_rowid must be NULL). */
 int hmj_hashjoin_build_probe(hmj_ctx* ctx, const hmj_relation* r_unsorted,
                              const hmj_relation* s_unsorted, const uint64_t* d_rvals,
                              const uint64_t* d_svals, uint64_t* h_hits, uint64_t* h_sum);
@@ -245,6 +253,27 @@ int hmj_dist_join_u64(hmj_ctx* ctx, const uint64_t* d_rkeys, size_t nr, uint32_t
 int hmj_dist_last_exchange(hmj_ctx* ctx, uint64_t* sent_pairs_remote, uint64_t* received_r,
                            uint64_t* received_s);
 int hmj_dist_teardown(hmj_ctx* ctx);
+
+/* ---- string keys over several GPUs: the key gather fused with the exchange (dist_strings.cu) --
+ * The rows of a relation travel to the GPU owning their hash range WITH their keys
+ * (partition_only's row movement, partitioned_hash.h:102-110).  setup allocates this rank's
+ * receive buffers for both relations (fixed capacities) and exports 6 IPC handles; connect takes
+ * all ranks' handles in rank order.  send: the rank's rows in send order (grouped by owner) --
+ * d_start/d_send_off from hmj_string_row_spans + a prefix sum -- are written straight into the
+ * owners' buffers over NVLink by ONE kernel (key bytes, row id, length); the h_* arrays say which
+ * send-order rows go to which owner and where this rank's block starts there (from the G x G count
+ * matrix).  The caller orders the ranks (stream-ordered barrier after the sends, and before the
+ * buffers are written again).  buffers: this rank's receive buffers. */
+int hmj_xchg_handle_bytes(void);
+int hmj_xchg_setup(hmj_ctx* ctx, int rank, int world, size_t rows_cap, size_t bytes_cap,
+                   unsigned char* handles_out);
+int hmj_xchg_connect(hmj_ctx* ctx, const unsigned char* all_handles);
+int hmj_xchg_send(hmj_ctx* ctx, int side, const uint8_t* d_chars, const uint64_t* d_start,
+                  const uint64_t* d_send_off, const uint32_t* d_rowid, const uint32_t* d_lens, size_t n,
+                  const uint64_t* h_part_first, const uint64_t* h_row_base, const uint64_t* h_byte_base);
+int hmj_xchg_buffers(hmj_ctx* ctx, int side, uint8_t** d_chars, uint32_t** d_rowid, uint32_t** d_lens,
+                     size_t* rows_cap, size_t* bytes_cap);
+int hmj_xchg_teardown(hmj_ctx* ctx);
 
 /* ---- benchmark relation generators on the device (datagen.cu; harness, not on the join path) --
  * The reference builds its inputs on the host with create_strvec (strgen.cc:28-61: ceil(sqrt(n))

@@ -110,20 +110,30 @@ def _rank_main(rank, world, port, rows_total, q):
         cdf = torch.from_numpy(datagen.zipf_cdf(n_keys, 1.0)).cuda()
         s_ids = gen.zipf_ids(cdf, per, seed=5, key_seed=9, row_base=rank * per)
         (roff, rchars), (soff, schars) = gen.keys(r_ids), gen.keys(s_ids)
-        joiner = DistJoin(ctx, rank, world)
-        m, (g_r, g_s) = joiner.join_strings(roff, rchars, soff, schars, want_pairs=True)
-        gathered = [None] * world
-        dist.all_gather_object(gathered, (g_r.cpu().numpy().view(np.uint32), g_s.cpu().numpy().view(np.uint32),
-                                          r_ids.cpu().numpy(), s_ids.cpu().numpy()))
-        if rank == 0:
-            a, b = canon(np.concatenate([g[0] for g in gathered]), np.concatenate([g[1] for g in gathered]))
-            all_r = np.concatenate([g[2] for g in gathered]).astype(np.uint64)
-            all_s = np.concatenate([g[3] for g in gathered]).astype(np.uint64)
-            x_r, x_s = canon(*expected_pairs(all_r, all_s))   # equal key id = equal key
-            ok = np.array_equal(a, x_r) and np.array_equal(b, x_s)
-            report.append(f"strings: world {world} {2 * n_keys} x {2 * n_keys} rows pairs {a.size} "
-                          f"expected {x_r.size} {'OK' if ok else 'MISMATCH'}")
-            assert ok, report[-1]
+        x_r = x_s = None
+        os.environ["HMJ_DIST_FUSED"] = "1"
+        # twice through the fused route (keys written into the owners' buffers by the gather kernel;
+        # the second join reuses the buffers), once through the NCCL route, once with buffers too
+        # small for the data (every rank falls back to NCCL together)
+        for tag, hint, joins in (("fused", 2 * n_keys, 2), ("nccl", 0, 1), ("fused, buffers too small", 1024, 1)):
+            joiner = DistJoin(ctx, rank, world, string_rows_hint=hint)
+            for rep in range(joins):
+                m, (g_r, g_s) = joiner.join_strings(roff, rchars, soff, schars, want_pairs=True)
+            assert joiner.xchg_joins == (joins if tag == "fused" else 0), (tag, joiner.xchg_joins)
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (g_r.cpu().numpy().view(np.uint32), g_s.cpu().numpy().view(np.uint32),
+                                              r_ids.cpu().numpy(), s_ids.cpu().numpy()))
+            if rank == 0:
+                a, b = canon(np.concatenate([g[0] for g in gathered]), np.concatenate([g[1] for g in gathered]))
+                if x_r is None:
+                    all_r = np.concatenate([g[2] for g in gathered]).astype(np.uint64)
+                    all_s = np.concatenate([g[3] for g in gathered]).astype(np.uint64)
+                    x_r, x_s = canon(*expected_pairs(all_r, all_s))   # equal key id = equal key
+                ok = np.array_equal(a, x_r) and np.array_equal(b, x_s)
+                report.append(f"strings ({tag}): world {world} {2 * n_keys} x {2 * n_keys} rows pairs {a.size} "
+                              f"expected {x_r.size} {'OK' if ok else 'MISMATCH'}")
+                assert ok, report[-1]
+            joiner.close()
         dist.barrier()
         ctx.close()
         dist.destroy_process_group()

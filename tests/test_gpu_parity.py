@@ -60,6 +60,26 @@ def test_hash_strgen_and_long_rows(ctx, oracle):
     assert np.array_equal(out, oracle.hash_strings(off, chars))
 
 
+def test_hash_pipelined_kernel_regular_and_irregular_tiles(ctx, oracle):
+    # >= 4 tiles of 1024 rows: the bulk-copy pipelined kernel.  Short rows (tiles staged in shared
+    # memory), long rows (tiles whose bytes do not fit: hashed from global memory), a mix of both in
+    # one column, empty rows at the end, and a row count that leaves a partial last tile.
+    rng = np.random.default_rng(5)
+    def rows(lens):
+        return [bytes(rng.integers(0, 256, size=int(ln), dtype=np.uint8)) for ln in lens]
+    cases = {
+        "short": rows(rng.integers(0, 30, size=9000)),
+        "long": rows(rng.integers(0, 400, size=6001)),
+        "mixed": rows(np.concatenate([rng.integers(0, 20, size=3000), rng.integers(100, 300, size=2500),
+                                      rng.integers(0, 20, size=3000), np.zeros(1500, np.int64)])),
+    }
+    for name, items in cases.items():
+        off, chars = datagen.strings_from_list(items)
+        chars = np.concatenate([chars, np.zeros(64, np.uint8)])
+        out = host(ctx.hash_strings(dev(off), dev(chars)), np.uint64)
+        assert np.array_equal(out, oracle.hash_strings(off, chars)), name
+
+
 def test_hash_u64_identity(ctx):
     k = np.random.default_rng(0).integers(0, 2 ** 64, size=100001, dtype=np.uint64)
     assert np.array_equal(host(ctx.hash_u64(dev(k)), np.uint64), k)
