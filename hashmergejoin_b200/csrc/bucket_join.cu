@@ -526,23 +526,29 @@ bucket_join_table_kernel(const BJArgs A) {
     }
     __syncthreads();  // the S hashes are dead from here on
   }
-  // ---- first matches: staged, then coalesced stores
+  // ---- first matches: staged, then coalesced stores.  A thread's pairs take consecutive staging
+  // slots and most threads hold exactly 8 of them (4096 R pairs over 512 threads), so the lanes
+  // of a warp would store with a stride of 8 words -- an 8-way bank conflict that was 27 % of the
+  // kernel's shared-memory wavefronts (profiles/r2s_join_table_digest.txt).  XOR-ing the low five
+  // index bits with the next five spreads such strides over all banks and keeps consecutive
+  // slots (the read-back below) conflict-free.
+  auto swz = [](uint32_t i) -> uint32_t { return i ^ ((i >> 5) & 31u); };
   {
     uint32_t off = f_off;
 #pragma unroll
     for (int k = 0; k < BJ_ITEMS; ++k) {
       if (cnt[k]) {
         const uint32_t sv = s_sv[hit[k]];
-        s_or[off] = rrow[k];
-        s_os[off] = sv;
+        s_or[swz(off)] = rrow[k];
+        s_os[swz(off)] = sv;
         ++off;
       }
     }
   }
   __syncthreads();
   for (uint32_t i = tid; i < F; i += BJ_THREADS) {
-    A.out_r[gbase + i] = s_or[i];
-    A.out_s[gbase + i] = s_os[i];
+    A.out_r[gbase + i] = s_or[swz(i)];
+    A.out_s[gbase + i] = s_os[swz(i)];
   }
 }
 
