@@ -24,6 +24,21 @@
 
 namespace {
 
+// 8-byte shared-memory load executed only where `p` holds; elsewhere the result is all ones
+__device__ __forceinline__ uint64_t lds64_if(bool p, const uint64_t* a) {
+  uint64_t v = ~0ull;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred q;\n\t"
+      "setp.ne.u32 q, %2, 0;\n\t"
+      "@q ld.shared.u64 %0, [%1];\n\t"
+      "}"
+      : "+l"(v)
+      : "r"((uint32_t)__cvta_generic_to_shared(a)), "r"((uint32_t)p)
+      : "memory");
+  return v;
+}
+
 constexpr int SEG_BINS = 4096;
 constexpr int SEG_BIN_LIMIT = 192;
 
@@ -188,11 +203,17 @@ segment_sort_kernel(uint64_t* __restrict__ keys, uint32_t* __restrict__ vals,
         const uint32_t d = (uint32_t)(rel >> s);
         const uint64_t me = ((rel & rem_mask) << IDX_BITS) | i;
         const uint32_t b0 = s_bin[d], c = s_bin[d + 1] - b0;
+        // The first four bin-mates without a branch, but each load PREDICATED on "this slot holds
+        // another pair of my bin": a bin has one pair on average, so three of four loads drop
+        // out and with them their share of the random-access bank conflicts (the unconditional
+        // form of this loop was 58 M of the kernel's 141 M shared-memory wavefronts at 64M pairs,
+        // profiles/r2t_segment_sort_*).  An unloaded word stays all ones, which no `me` is.
+        const uint32_t own = slot[k];
         uint32_t r = 0;
 #pragma unroll
         for (uint32_t j = 0; j < 4; ++j) {
-          const uint64_t o = s_keys[b0 + j];  // may read past the bin: masked by j < c
-          r += (j < c && o < me) ? 1u : 0u;
+          const uint64_t o = lds64_if(j < c && j != own, s_keys + b0 + j);
+          r += (o < me) ? 1u : 0u;
         }
         for (uint32_t j = 4; j < c; ++j) r += (s_keys[b0 + j] < me) ? 1u : 0u;
         slot[k] = (uint16_t)(b0 + r);
