@@ -157,7 +157,8 @@ template <int THREADS>
 struct UtCfg {
   static constexpr int TILE = THREADS * UT_ITEMS;
   static constexpr int BINS = THREADS > 512 ? 512 : 256;   // most bins a level of this shape cuts
-  static constexpr size_t BUF_BYTES = (size_t)TILE * 12;
+  static constexpr int SLACK = 64;  // slots behind the tile: room to start runs at padded positions (DIST)
+  static constexpr size_t BUF_BYTES = (size_t)(TILE + SLACK) * 12;
   // buffers, [cnt][off][gbase] per bin, region ends and starts (<= 512 regions), scan, bars, peers
   static constexpr size_t SMEM = 2 * BUF_BYTES + 3 * BINS * 4 + 2 * 512 * 4 + 32 * 4 + 64 + 16 * 8;
 };
@@ -290,7 +291,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       const uint32_t bytes = UT_TILE * 8 + (vals_in ? UT_TILE * 4 : 0);
       mbar_expect_tx(&s_bar[b], bytes);
       bulk_load(buf, keys_in + in_base, UT_TILE * 8, &s_bar[b]);
-      if (vals_in) bulk_load(buf + UT_TILE * 8, vals_in + in_base, UT_TILE * 4, &s_bar[b]);
+      if (vals_in) bulk_load(buf + (UT_TILE + Cfg::SLACK) * 8, vals_in + in_base, UT_TILE * 4, &s_bar[b]);
     }
     return true;
   };
@@ -322,7 +323,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       return;
     }
     uint64_t* b_keys = reinterpret_cast<uint64_t*>(smem_tma + (size_t)b * UT_BUF_BYTES);
-    uint32_t* b_vals = reinterpret_cast<uint32_t*>(b_keys + UT_TILE);
+    uint32_t* b_vals = reinterpret_cast<uint32_t*>(b_keys + UT_TILE + Cfg::SLACK);
     if (tid < bins) s_cnt[tid] = 0;
     if (pending_cur) {
       mbar_wait(&s_bar[b], phase[b]);
@@ -378,8 +379,26 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) wt += __shfl_xor_sync(0xffffffffu, wt, o);
       if (tid < bins) s_off[tid] = wt + x - c;
+      if (DIST && tid < bins) s_gbase[tid] = old;  // (the bulk-store path below reads it back)
     }
     __syncthreads();  // s_off ready; every thread holds its keys and row ids in registers
+    // DIST with few regions: a region's run leaves as ONE bulk async store per column
+    // (cp.async.bulk shared -> peer global), which needs source and destination equally aligned
+    // to 16 bytes.  The run of region d therefore starts at a tile position congruent to its
+    // first global slot modulo 4 pairs (up to 3 slots of padding per region, in the slack behind
+    // the tile).
+    const bool bulk_out = DIST && peers.bulk && bins <= 16;
+    if (bulk_out) {
+      if (tid == 0) {
+        uint32_t run = 0;
+        for (int d = 0; d < bins; ++d) {
+          run += (s_gbase[d] - run) & 3u;
+          s_off[d] = run;
+          run += s_cnt[d];
+        }
+      }
+      __syncthreads();
+    }
 
 #pragma unroll
     for (int k = 0; k < UT_ITEMS; ++k) {
@@ -393,7 +412,7 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
     bool over = stray;
     if (tid < bins) {
       over |= c != 0 && (old > out_cap || c > out_cap - old);
-      s_gbase[tid] = bucket * out_cap + old - s_off[tid];
+      if (!bulk_out) s_gbase[tid] = bucket * out_cap + old - s_off[tid];  // (bulk: keeps `old`)
     }
     if (__syncthreads_or(over)) {
       if (tid == 0) atomicOr(flag, 1u);
@@ -401,6 +420,42 @@ bucket_scatter_tma_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* 
       return;
     }
     const uint32_t live = valid - lo;  // the permuted pairs sit at [0, live)
+    if (bulk_out) {
+      // warp d sends region d: head and tail pairs (to the 4-pair boundaries of the destination)
+      // with plain stores, everything between with two bulk stores
+      if (warp < bins) {
+        const uint32_t d = (uint32_t)warp, cnt_d = s_cnt[d];
+        if (cnt_d) {
+          const uint32_t p0 = s_off[d], old_d = s_gbase[d];
+          const uint32_t sub = (d & ((1u << peers.own_bits) - 1)) * (uint32_t)peers.world + (uint32_t)peers.rank;
+          const uint32_t g0 = sub * out_cap + old_d;
+          const uint32_t o = d >> peers.own_bits;
+          const uint32_t head = min(cnt_d, (4u - (g0 & 3u)) & 3u);
+          const uint32_t mid = (cnt_d - head) & ~3u;
+          const uint32_t tail = cnt_d - head - mid;
+          if ((uint32_t)lane < head) {
+            s_pk[o][g0 + lane] = b_keys[p0 + lane];
+            s_pv[o][g0 + lane] = b_vals[p0 + lane];
+          }
+          if ((uint32_t)lane < tail) {
+            s_pk[o][g0 + head + mid + lane] = b_keys[p0 + head + mid + lane];
+            s_pv[o][g0 + head + mid + lane] = b_vals[p0 + head + mid + lane];
+          }
+          if (lane == 0 && mid) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(s_pk[o] + g0 + head),
+                         "r"(smem_u32(b_keys + p0 + head)), "r"(mid * 8u)
+                         : "memory");
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(s_pv[o] + g0 + head),
+                         "r"(smem_u32(b_vals + p0 + head)), "r"(mid * 4u)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            // the buffer is refilled after the barrier below: its bytes must have been read by then
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          }
+        }
+      }
+    } else
 #pragma unroll 4
     for (uint32_t i = tid; i < live; i += UT_THREADS) {
       const uint64_t kk = b_keys[i];

@@ -195,6 +195,7 @@ struct hmj_peer_regions {
   uint32_t* counts[8];  // per owner: pairs in sub-region (region * world + source rank)
   int own_bits;         // log2(regions per GPU)
   int world, rank;      // GPUs of the job, this GPU
+  int bulk;             // runs leave as bulk async stores (HMJ_DIST_BULK, default on)
 };
 int hmj_scatter_level1_dist(hmj_ctx* ctx, cudaStream_t st, const uint64_t* keys_in, size_t n,
                             uint32_t iota_base, int shift, int bits, uint32_t out_cap,

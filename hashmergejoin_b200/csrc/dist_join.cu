@@ -219,6 +219,8 @@ extern "C" int hmj_dist_connect(hmj_ctx* ctx, const unsigned char* all_handles) 
     d->peers[s].own_bits = d->own_bits;
     d->peers[s].world = d->world;
     d->peers[s].rank = d->rank;
+    const char* e = getenv("HMJ_DIST_BULK");
+    d->peers[s].bulk = !(e && atoi(e) == 0);
   }
   for (int r = 0; r < d->world; ++r) {
     void* ptrs[HANDLES_PER_RANK];
