@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Turns the raw artefacts of scripts/gpu_round1_measure.sh (gpurun_out/<tag>_*) into the small
+"""Turns the raw artefacts of scripts/gpu_round1_measure.sh (round 1; removed) (gpurun_out/<tag>_*) into the small
 tracked summaries under profiles/:
   <tag>_bench_c3.json / <tag>_bench_reference.json   the bench lines as printed
   <tag>_launches_c3.csv + <tag>_launch_shares.txt    ncu launch list and per-kernel share of step
