@@ -10,7 +10,9 @@ and the line says which one ran (`config.path`):
         one or two bucket-scatter levels and joined bucket by bucket in shared memory (uniform
         hashes: c1, c3, c4);
   "onesweep sort + merge-path join"        stable LSD passes + merge join (skewed / duplicated
-        hashes: the Zipf side of c5, c3-dense; forced by c3-sortmerge).
+        hashes: the Zipf side of c5; forced by c3-onesweep);
+  "bucket-scatter sort + merge-path join"  both relations sorted by scatter levels + an
+        in-shared-memory finish, then merge-joined (c3-sortmerge, or hmj_set_join_order).
 Workloads (BASELINE.json configs):
   c3 (default, N=1)  256M x 256M u64 keys, 1:1                         configs[2]
   c4 (default, N>1)  1B x 1B u64 keys over N GPUs, strong scaling      configs[3]
@@ -20,7 +22,8 @@ Workloads (BASELINE.json configs):
   c2   hash + sort of 64M strgen strings (hmj_hash_sort_strings)       configs[1]
   c5   strgen strings, build keys twice, Zipf(1.0) probe; --rows sets rows per side (default
        64M on one GPU; 512M x 512M = configs[4] with --gpus 8)
-  c3-dense      c3 with keys 0..N-1 (identity hash: every row in one bucket of the top bits)
+  c3-dense      c3 with keys 0..N-1 (identity hash: the top 36 hash bits are all zero; the sample
+                finds the shared prefix and the bucket plan skips it)
   c3-sortmerge  c3 with both relations sorted and merge-joined (HMJ_JOIN_UNIFORM=0)
   c3-onesweep   ... and the sort done by stable LSD passes (HMJ_SORT_UNIFORM=0): the literal
                 hash -> onesweep radix sort -> merge-path join pipeline
