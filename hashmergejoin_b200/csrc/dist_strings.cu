@@ -31,8 +31,8 @@ struct xs_peers {
 
 constexpr int XS_THREADS = 256;
 constexpr int XS_ROWS = 1024;           // send-order rows per CTA (all for one owner)
-constexpr int XS_CHUNK = 40 * 1024;     // key bytes a CTA stages (mean 18 B per key: 18 KB)
-constexpr size_t XS_SMEM = (size_t)(XS_ROWS + 2) * 8 + XS_CHUNK + 32;
+constexpr int XS_CHUNK = 32 * 1024;     // key bytes a CTA stages (mean 18 B per key: 18 KB)
+constexpr size_t XS_SMEM = 2 * (size_t)(XS_ROWS + 2) * 8 + XS_CHUNK + 32;
 
 // One CTA = up to 1024 consecutive send-order rows of ONE owner.  Their key bytes are contiguous in
 // the owner's buffer, so the CTA gathers them (random rows of the local column) into shared
@@ -46,7 +46,8 @@ xchg_send_kernel(const uint8_t* __restrict__ chars, const uint64_t* __restrict__
                  const uint32_t* __restrict__ lens, int world, const xs_peers P) {
   extern __shared__ __align__(16) unsigned char xs_raw[];
   uint64_t* s_off = reinterpret_cast<uint64_t*>(xs_raw);                 // [rows + 1]
-  unsigned char* s_buf = xs_raw + (size_t)(XS_ROWS + 2) * 8;             // [XS_CHUNK + 32]
+  uint64_t* s_start = s_off + XS_ROWS + 2;                               // [rows] first byte of a key
+  unsigned char* s_buf = xs_raw + 2 * (size_t)(XS_ROWS + 2) * 8;         // [XS_CHUNK + 32]
   const int tid = threadIdx.x;
   int g = 0;
 #pragma unroll
@@ -57,6 +58,7 @@ xchg_send_kernel(const uint8_t* __restrict__ chars, const uint64_t* __restrict__
   if (i0 >= i1) return;
   const uint32_t rows = (uint32_t)(i1 - i0);
   for (uint32_t r = tid; r <= rows; r += XS_THREADS) s_off[r] = send_off[i0 + r];
+  for (uint32_t r = tid; r < rows; r += XS_THREADS) s_start[r] = start[i0 + r];
   const uint64_t part_off = send_off[P.part_first[g]];
   __syncthreads();
   const uint64_t base = s_off[0], total = s_off[rows] - base;
@@ -72,11 +74,39 @@ xchg_send_kernel(const uint8_t* __restrict__ chars, const uint64_t* __restrict__
   if (total <= (uint64_t)XS_CHUNK) {
     // the chunk sits in shared memory at the same offset modulo 16 as in the owner's buffer
     const uint32_t pad = (uint32_t)(reinterpret_cast<uintptr_t>(dst) & 15);
+    // Four rows per 8-lane group at a time, all their byte loads issued before the first store: a
+    // row's key sits at a random place of the column, and with one row in flight per group the
+    // CTA spent its time waiting for one DRAM round trip after the other.
     const int lane = tid & 7;
-    for (uint32_t r = tid >> 3; r < rows; r += XS_THREADS / 8) {
-      const uint32_t o = (uint32_t)(s_off[r] - base), len = (uint32_t)(s_off[r + 1] - s_off[r]);
-      const uint8_t* src = chars + start[i0 + r];
-      for (uint32_t k = lane; k < len; k += 8) s_buf[pad + o + k] = src[k];
+    constexpr int GROUPS = XS_THREADS / 8, Q = 4, T = 4;  // T x 8 = 32 bytes per row in registers
+    for (uint32_t rb = tid >> 3; rb < rows; rb += GROUPS * Q) {
+      uint8_t v[Q][T];
+      uint32_t o[Q], len[Q];
+      const uint8_t* src[Q];
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+        const uint32_t r = rb + q * GROUPS;
+        len[q] = 0;
+        if (r < rows) {
+          o[q] = (uint32_t)(s_off[r] - base);
+          len[q] = (uint32_t)(s_off[r + 1] - s_off[r]);
+          src[q] = chars + s_start[r];
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const uint32_t k = lane + 8 * t;
+            v[q][t] = k < len[q] ? src[q][k] : (uint8_t)0;
+          }
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < Q; ++q) {
+#pragma unroll
+        for (int t = 0; t < T; ++t) {
+          const uint32_t k = lane + 8 * t;
+          if (k < len[q]) s_buf[pad + o[q] + k] = v[q][t];
+        }
+        for (uint32_t k = lane + 8 * T; k < len[q]; k += 8) s_buf[pad + o[q] + k] = src[q][k];
+      }
     }
     __syncthreads();
     const uint32_t n = (uint32_t)total;
@@ -92,7 +122,7 @@ xchg_send_kernel(const uint8_t* __restrict__ chars, const uint64_t* __restrict__
     const int lane = tid & 7;
     for (uint32_t r = tid >> 3; r < rows; r += XS_THREADS / 8) {
       const uint64_t o = s_off[r] - base, len = s_off[r + 1] - s_off[r];
-      const uint8_t* src = chars + start[i0 + r];
+      const uint8_t* src = chars + s_start[r];
       for (uint64_t k = lane; k < len; k += 8) dst[o + k] = src[k];
     }
   }
