@@ -271,7 +271,7 @@ __device__ __forceinline__ uint64_t jd_load(const uint64_t* p) {
 //                over per-tile descriptors, write the pairs if they fit in `cap`; tile_counts are
 //                published too, so an overflowing join can finish with scan + JOIN_WRITE.
 template <int KIND, int MODE>
-__global__ void __launch_bounds__(JOIN_THREADS)
+__global__ void __launch_bounds__(JOIN_THREADS, 2)
 join_tile_kernel(const JoinArgs A) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   uint64_t* s_h = reinterpret_cast<uint64_t*>(smem_raw);               // R hashes then S hashes, padded
@@ -537,16 +537,79 @@ join_tile_kernel(const JoinArgs A) {
               }
             }
           }
+          if (KIND == HMJ_KEY_STRING) {
+            // String keys: the first two candidates of two elements at a time, with the loads of
+            // all six keys staged (offsets, then bytes, then the comparison) instead of one
+            // dependent chain per candidate (join_device.cuh).  Further candidates, empty keys
+            // and keys longer than 32 bytes take the one-by-one check.
 #pragma unroll
-          for (int g = 0; g < G; ++g) {
-            if (nc[g] == 0) continue;
-            uint64_t o = off[g];
-            for (uint32_t t = 0; t < nc[g]; ++t) {
-              const uint32_t sr = t == 0 ? srow[g] : A.sr[lb[g] + t];
-              if (KIND == HMJ_KEY_STRING && !cand_ok<KIND>(A, rrow[g], sr)) continue;
-              A.out_r[o] = rrow[g];
-              A.out_s[o] = sr;
-              ++o;
+            for (int h0 = 0; h0 < G; h0 += 2) {
+              uint32_t sr1[2];
+              hmj_key_span sa[2], sb0[2], sb1[2];
+              bool fast[2];
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int g = h0 + h;
+                sr1[h] = 0;
+                fast[h] = false;
+                if (nc[g]) {
+                  sa[h] = key_span_of(A.roff, rrow[g]);
+                  sb0[h] = key_span_of(A.soff, srow[g]);
+                  sr1[h] = nc[g] > 1 ? A.sr[lb[g] + 1] : srow[g];
+                }
+              }
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int g = h0 + h;
+                if (nc[g]) {
+                  sb1[h] = key_span_of(A.soff, sr1[h]);
+                  fast[h] = sa[h].len >= 1 && sa[h].len <= 32;
+                }
+              }
+              hmj_key_words ka[2], kb0[2], kb1[2];
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                if (fast[h]) {
+                  key_words_load(A.rchars, sa[h], &ka[h]);
+                  // (a candidate of another length cannot match: load nothing for it)
+                  if (sb0[h].len == sa[h].len) key_words_load(A.schars, sb0[h], &kb0[h]);
+                  if (sb1[h].len == sa[h].len) key_words_load(A.schars, sb1[h], &kb1[h]);
+                }
+              }
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int g = h0 + h;
+                if (nc[g] == 0) continue;
+                uint64_t o = off[g];
+                for (uint32_t t = 0; t < nc[g]; ++t) {
+                  const uint32_t sr = t == 0 ? srow[g] : t == 1 ? sr1[h] : A.sr[lb[g] + t];
+                  bool ok;
+                  if (fast[h] && t < 2) {
+                    const hmj_key_span& sb = t == 0 ? sb0[h] : sb1[h];
+                    ok = sb.len == sa[h].len &&
+                         key_words_equal(ka[h], t == 0 ? kb0[h] : kb1[h], (uint32_t)sa[h].len);
+                    if (!ok && A.optimistic) *reinterpret_cast<volatile uint32_t*>(A.collision) = 1u;
+                  } else {
+                    ok = cand_ok<KIND>(A, rrow[g], sr);
+                  }
+                  if (!ok) continue;
+                  A.out_r[o] = rrow[g];
+                  A.out_s[o] = sr;
+                  ++o;
+                }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int g = 0; g < G; ++g) {
+              if (nc[g] == 0) continue;
+              uint64_t o = off[g];
+              for (uint32_t t = 0; t < nc[g]; ++t) {
+                const uint32_t sr = t == 0 ? srow[g] : A.sr[lb[g] + t];
+                A.out_r[o] = rrow[g];
+                A.out_s[o] = sr;
+                ++o;
+              }
             }
           }
         }
