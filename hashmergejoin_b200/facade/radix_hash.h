@@ -7,8 +7,9 @@
 //   radix_hash::radix_inplace_par(dst,n,num_threads[,bits])           :589-654
 //
 // Input items are pair-like (`->first` key, `->second` value, reference :343-344); dst items are
-// std::tuple<std::size_t, Key, Value>.  num_threads and partition_bits are accepted and ignored:
-// the GPU is the thread pool and the digit width is the kernel's.  Result: hash column ascending
+// std::tuple<std::size_t, Key, Value>.  partition_bits is accepted and ignored (the digit width is
+// the kernel's); num_threads is the number of HOST threads used for what stays on the host
+// (flattening keys, writing the sorted tuples) -- the sort itself runs on the GPU.  Result: hash column ascending
 // (what the reference's tests pin); inside an equal-hash run rows keep their input order (the
 // reference leaves that order unspecified).
 #ifndef RADIX_HASH_H
@@ -37,9 +38,12 @@ struct tuple_key {
 template <typename Key, typename Value, typename Hash = std::hash<Key>,
           typename BidirectionalIterator, typename RandomAccessIterator>
 void radix_non_inplace_par(BidirectionalIterator begin, BidirectionalIterator end,
-                           RandomAccessIterator dst, int /*num_threads*/, int /*partition_bits*/) {
+                           RandomAccessIterator dst, int num_threads, int /*partition_bits*/) {
+  // num_threads: the host threads that flatten the keys and write the sorted tuples (the sort
+  // itself runs on the GPU)
+  const int threads = num_threads > 0 ? num_threads : 1;
   const hmj::detail::KeyColumns cols =
-      hmj::detail::flatten<Key, Hash>(begin, end, detail::first_of());
+      hmj::detail::flatten<Key, Hash>(begin, end, detail::first_of(), threads);
   hmj::detail::PinnedArray<uint64_t> hash;
   hmj::detail::PinnedArray<uint32_t> rowid;
   hmj::detail::hash_sort<Key, Hash>(cols, &hash, &rowid);
@@ -48,11 +52,13 @@ void radix_non_inplace_par(BidirectionalIterator begin, BidirectionalIterator en
   std::vector<const Item*> rows;
   rows.reserve(cols.n);
   for (BidirectionalIterator it = begin; it != end; ++it) rows.push_back(&*it);
-  for (std::size_t i = 0; i < cols.n; ++i) {
-    const Item& src = *rows[rowid[i]];
-    dst[i] = std::tuple<std::size_t, Key, Value>(static_cast<std::size_t>(hash[i]), src.first,
-                                                src.second);
-  }
+  hmj::detail::parallel_slices(cols.n, threads, [&](int, std::size_t lo, std::size_t hi) {
+    for (std::size_t i = lo; i < hi; ++i) {
+      const Item& src = *rows[rowid[i]];
+      dst[i] = std::tuple<std::size_t, Key, Value>(static_cast<std::size_t>(hash[i]), src.first,
+                                                  src.second);
+    }
+  });
 }
 
 template <typename Key, typename Value, typename Hash = std::hash<Key>,
