@@ -83,7 +83,7 @@ int join_u64_host_chunked(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, cons
                           uint64_t* h_num_pairs, uint64_t* d_r, uint64_t* d_s, int* done) {
   *done = 0;
   const int chunks = host_chunks_from_env();
-  const hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, 0);
+  hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, 0);
   const char* e = getenv("HMJ_JOIN_UNIFORM");
   const bool eligible = chunks > 1 && p.levels != 0 && nr >= ((size_t)chunks << 16) && ns > 0 &&
                         !(e && atoi(e) == 0) && !ctx->hash_order;
@@ -122,6 +122,28 @@ int join_u64_host_chunked(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, cons
   dcap = ctx->ws[WS_OUT_R].bytes / 4;
   if (ctx->ws[WS_OUT_S].bytes / 4 < dcap) dcap = ctx->ws[WS_OUT_S].bytes / 4;
   HMJ_TRY(hmj_fill_async(ctx, d_total, 0, 32, st));
+  // The plan comes from a sample of S and of R's FIRST chunk, taken as soon as both have landed
+  // (the other chunks keep arriving meanwhile): a hash prefix all sampled keys share is skipped
+  // -- dense integer keys -- and checked on every row by level 1 of every chunk; a relation the
+  // sample finds skewed ends the attempt before anything is scattered.
+  const size_t n0 = nr < per ? nr : per;
+  if (nr + ns >= ((size_t)1 << 22) && n0 >= 32768 && ns >= 32768) {
+    HMJ_CUDA(ctx, cudaEventSynchronize(ctx->copy_events[0]));
+    int skewed = 0;
+    HMJ_TRY(hmj_sample_plan(ctx, d_r, n0, d_s, ns, &p, &skewed));
+    p = skewed ? hmj_uniform_plan() : p;
+    if (p.levels != 0 && (nr > ns ? nr : ns) != (n0 > ns ? n0 : ns)) {
+      // (the sample planned for chunk 0's size: keep its prefix, take the bucket count of the join)
+      hmj_uniform_plan q = hmj_uniform_plan_for(nr > ns ? nr : ns, p.skip);
+      q.check_prefix = p.check_prefix;
+      q.prefix = p.prefix;
+      p = q;
+    }
+    if (p.levels == 0) {
+      HMJ_CUDA(ctx, cudaStreamSynchronize(cin));
+      return HMJ_OK;
+    }
+  }
   // S into its buckets
   hmj_uniform_buckets Sb, Rb;
   HMJ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->copy_events[chunks], 0));

@@ -859,6 +859,16 @@ def test_host_join_in_chunks_and_its_fallbacks(ctx, oracle):
     assert np.array_equal(rk[o_r], sk3[o_s])
     w = (o_r.astype(np.uint64) << np.uint64(32)) | o_s.astype(np.uint64)
     assert np.unique(w).size == 3 * n
+    # dense keys 0..N-1 through the host entry: the sample of S and of R's first chunk finds the
+    # shared prefix, so the chunked plan (not the copy-join-copy fallback) runs
+    # (a power-of-two range: 0..3M-1 would leave a quarter of the buckets empty and overfill the rest)
+    rng = np.random.default_rng(21)
+    nd = 1 << 22
+    dk_r, dk_s = rng.permutation(nd).astype(np.uint64), rng.permutation(nd).astype(np.uint64)
+    d_r, d_s = np.zeros(nd, np.uint32), np.zeros(nd, np.uint32)
+    assert ctx.join_u64_host(dk_r, dk_s, d_r, d_s) == nd
+    assert ctx.timings()["bucket_join"] == 1 and ctx.timings()["scatter_levels"] > 4, "dense keys left the chunked plan"
+    _check_pairs_1to1(dk_r, dk_s, d_r, d_s)
     # a capacity that is too small is reported, with the number of pairs
     with pytest.raises(hmj.HmjError) as ei:
         ctx.join_u64_host(rk, sk, out_r[: n // 2], out_s[: n // 2])
