@@ -312,6 +312,19 @@ class Context:
                                                    bits, _dptr(oh), _dptr(orow), _dptr(offs)))
         return oh, orow, offs
 
+    def partition_pairs_noalloc(self, hash_, rowid, bits, out, rowid_base=0):
+        """partition_pairs for callers that may not allocate device memory: the scratch is a fixed
+        array inside the library (include/hmj.h, hmj_partition_pairs_noalloc), `out` =
+        (hash_out[n] i64, rowid_out[n] i32, offsets[(1<<bits)+1] i64) is the caller's, and at most
+        NOALLOC_MAX_ROWS rows are taken.  Nothing is allocated here either."""
+        oh, orow, offs = out
+        self._ck(self.lib.hmj_partition_pairs_noalloc(self.h, _dptr(hash_), _dptr(rowid), rowid_base,
+                                                      hash_.numel(), bits, _dptr(oh), _dptr(orow),
+                                                      _dptr(offs)))
+        return oh, orow, offs
+
+    NOALLOC_MAX_ROWS = 1 << 24
+
     # ---- A7 hash-join baseline
     def hashjoin_build_probe(self, R, S, rvals=None, svals=None):
         hits, sm = C.c_uint64(), C.c_uint64()

@@ -18,6 +18,8 @@
 //       shared memory in tile-sorted order so every digit bin is written as a contiguous run.
 // Algorithmic bytes per pair: histogram 8; each executed pass 12 read + 12 written (the first
 // pass of an iota-row-id sort reads 8).
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -977,4 +979,98 @@ extern "C" int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash,
   const uint32_t epoch = ++ctx->lb_epoch;
   return launch_pass<256, 16, 3>(ctx, d_hash, d_rowid, d_hash_out, d_rowid_out, n32, 64 - bits,
                                  d_hist, d_lb, d_counters, epoch, rowid_base);
+}
+
+// ---------------------------------------------------------------- partitioning without allocation
+// hmj_partition_pairs_noalloc: the stable partition of hmj_partition_pairs_base with its scratch
+// (digit histogram, tile counter, look-back descriptors) in a fixed array of device memory that
+// the library carries itself, for callers that may not call cudaMalloc (code under CUDA graph
+// capture, serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The existing entry points are untouched.
+//   * The array is per GPU (every GPU that loads the library holds its NOALLOC_BYTES until the
+//     process exits) and shared by every call on that GPU: it keeps the last call's contents, so
+//     each call clears the words that must start at zero (histogram, counter, the descriptors of
+//     the tiles it will use), in stream order before the kernels that use them.  Calls that
+//     overlap on one GPU (two contexts / two streams) race on it: serialise them.
+//   * The first call per GPU resolves the array's device address (cudaGetSymbolAddress -- the
+//     name `g_noalloc_scratch` in host code is only a stand-in for it); make that call (n = 0 is
+//     enough) before a region that must not touch the driver's allocator, e.g. a graph capture.
+//   * No cudaMalloc / cudaFree / workspace growth, no profiling events: kernels only.
+namespace {
+constexpr size_t NOALLOC_MAX_ROWS = size_t(1) << 24;  // == HMJ_NOALLOC_MAX_ROWS (include/hmj.h)
+constexpr size_t NOALLOC_TILE = OnesweepCfg<256, 16>::TILE;
+constexpr size_t NOALLOC_MAX_TILES = (NOALLOC_MAX_ROWS + NOALLOC_TILE - 1) / NOALLOC_TILE;
+constexpr size_t NOALLOC_HIST_WORDS = NUM_PASSES * RADIX + 2 * NUM_PASSES;
+constexpr size_t NOALLOC_HIST_BYTES = (NOALLOC_HIST_WORDS * 4 + 255) & ~size_t(255);
+constexpr size_t NOALLOC_LB_BYTES = NOALLOC_MAX_TILES * RADIX * 8;
+constexpr size_t NOALLOC_BYTES = NOALLOC_HIST_BYTES + NOALLOC_LB_BYTES;  // 8 MiB + 8.25 KiB
+static_assert(NOALLOC_MAX_ROWS == HMJ_NOALLOC_MAX_ROWS, "header and kernel file disagree on the limit");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES];  // device address of the array, per GPU
+
+// device address of this GPU's copy of the array (the device must be current)
+int noalloc_scratch(hmj_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+    return hmj_fail(ctx, HMJ_EARG, "hmj_partition_pairs_noalloc: device ordinal beyond 63", __FILE__, __LINE__);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_ptr[ctx->device]) {
+    void* p = nullptr;
+    HMJ_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255) != 0)
+      return hmj_fail(ctx, HMJ_ECUDA, "hmj_partition_pairs_noalloc: no usable address for the scratch array", __FILE__, __LINE__);
+    g_noalloc_ptr[ctx->device] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[ctx->device];
+  return HMJ_OK;
+}
+}  // namespace
+
+extern "C" int hmj_partition_pairs_noalloc(hmj_ctx* ctx, const uint64_t* d_hash,
+                                           const uint32_t* d_rowid, uint32_t rowid_base, size_t n,
+                                           int bits, uint64_t* d_hash_out, uint32_t* d_rowid_out,
+                                           uint64_t* d_part_offsets) {
+  if (!ctx) return HMJ_EARG;
+  HMJ_ARG(ctx, bits >= 1 && bits <= 8 && d_part_offsets);
+  if (n > NOALLOC_MAX_ROWS)
+    return hmj_fail(ctx, HMJ_EARG,
+                    "hmj_partition_pairs_noalloc: n exceeds HMJ_NOALLOC_MAX_ROWS (16777216 rows): the fixed "
+                    "scratch array holds no more; use hmj_partition_pairs_base",
+                    __FILE__, __LINE__);
+  HMJ_ARG(ctx, n == 0 || (d_hash && d_hash_out && d_rowid_out));
+  HMJ_ARG(ctx, n == 0 || (d_hash != d_hash_out && (d_rowid == nullptr || d_rowid != d_rowid_out)));
+  HMJ_CUDA(ctx, cudaSetDevice(ctx->device));
+  unsigned char* scratch = nullptr;
+  HMJ_TRY(noalloc_scratch(ctx, &scratch));
+  cudaStream_t st = ctx->stream;
+  const int bins = 1 << bits;
+  const uint32_t n32 = (uint32_t)n;
+  uint32_t* d_hist = reinterpret_cast<uint32_t*>(scratch);
+  uint32_t* d_skip = d_hist + NUM_PASSES * RADIX;
+  uint32_t* d_counters = d_skip + NUM_PASSES;
+  uint64_t* d_lb = reinterpret_cast<uint64_t*>(scratch + NOALLOC_HIST_BYTES);
+  const size_t tiles = hmj_div_up(n, NOALLOC_TILE);
+  // what the last call left behind and this one needs at zero
+  HMJ_TRY(hmj_fill_async(ctx, d_hist, 0, NOALLOC_HIST_WORDS * sizeof(uint32_t), st));
+  HMJ_TRY(hmj_fill_async(ctx, d_lb, 0, tiles * RADIX * 8, st));
+  if (n) {
+    const int grid = (int)min(hmj_div_up(n, PART_THREADS * 8), (size_t)ctx->num_sms * 4);
+    partition_count_kernel<uint32_t><<<grid, PART_THREADS, RADIX * 4, st>>>(d_hash, n, 64 - bits, RADIX, d_hist, 1);
+    HMJ_LAUNCHED(ctx);
+  }
+  radix_scan_kernel<<<1, RADIX, 0, st>>>(d_hist, n32, d_skip);
+  HMJ_LAUNCHED(ctx);
+  partition_offsets_kernel<<<(bins + 1 + 255) / 256, 256, 0, st>>>(d_hist, bins, n32, d_part_offsets);
+  HMJ_LAUNCHED(ctx);
+  if (n == 0) return HMJ_OK;
+  using Cfg = OnesweepCfg<256, 16>;
+  HMJ_CUDA(ctx, cudaFuncSetAttribute(onesweep_pass_kernel<256, 16, 3, 0, LB_WINDOW_DEFAULT>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+  onesweep_pass_kernel<256, 16, 3, 0, LB_WINDOW_DEFAULT><<<(unsigned)tiles, 256, Cfg::SMEM_BYTES, st>>>(
+      d_hash, d_rowid, d_hash_out, d_rowid_out, n32, 64 - bits, d_hist, d_lb, d_counters, 1u, rowid_base);
+  HMJ_LAUNCHED(ctx);
+  return HMJ_OK;
 }

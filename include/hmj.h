@@ -218,6 +218,21 @@ int hmj_partition_pairs_base(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_
                              uint32_t* d_rowid_out, uint64_t* d_part_offsets);
 int hmj_partition_counts_host(hmj_ctx* ctx, const uint64_t* h_hash, size_t n, int bits,
                               uint64_t* h_counts);
+/* hmj_partition_pairs_base for callers that may not allocate device memory (code under CUDA
+ * graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+ * reference.  Same arguments, same result; the
+ * scratch (digit histogram, tile counter, look-back descriptors) lives in a fixed 8.01 MiB
+ * array of device memory inside the library (held by every GPU that loads the library until the
+ * process exits), so n is limited to HMJ_NOALLOC_MAX_ROWS: a larger n fails with HMJ_EARG and a
+ * message naming the limit.  The call launches kernels on the context's stream and calls no
+ * cudaMalloc / cudaFree and no allocating library routine; the first call per GPU looks up the
+ * array's address (make it -- n = 0 is enough -- before a region that must not reach the
+ * driver).  All calls on one GPU share the array: each clears what it needs at zero, and calls
+ * that overlap on the GPU (two contexts or streams) race -- serialise them. */
+#define HMJ_NOALLOC_MAX_ROWS ((size_t)1 << 24)
+int hmj_partition_pairs_noalloc(hmj_ctx* ctx, const uint64_t* d_hash, const uint32_t* d_rowid,
+                                uint32_t rowid_base, size_t n, int bits, uint64_t* d_hash_out,
+                                uint32_t* d_rowid_out, uint64_t* d_part_offsets);
 
 /* ---- A7: hash-join baseline (build/probe) -------------------------------------------- */
 /* replaces the loops of BM_hash_join_raw (hashjoin_bench.cc:47-53): build an open-addressing
