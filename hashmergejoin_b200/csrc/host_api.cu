@@ -60,13 +60,19 @@ int ensure_copy_streams(hmj_ctx* ctx, size_t events) {
   return HMJ_OK;
 }
 
-int host_chunks_from_env() {
-  static const int v = [] {
-    const char* e = getenv("HMJ_HOST_CHUNKS");
-    const int c = e ? atoi(e) : 8;
+// Chunks of R per host-buffer join.  More chunks shorten the tail (the last chunk's scatter, join
+// and copy out, which nothing overlaps) and cost a host round trip each: at 256M rows 4 / 8 / 12 /
+// 16 / 24 / 32 chunks take 94.3 / 90.0 / 89.0 / 88.6 / 88.7 / 90.1 ms (profiles/r2z6_e2e_chunks.txt),
+// so 16, with chunks of at least 512K rows.  HMJ_HOST_CHUNKS overrides; read per call so that one
+// process can sweep it (scripts/e2e_chunks.py).
+int host_chunks_for(size_t nr) {
+  const char* e = getenv("HMJ_HOST_CHUNKS");
+  if (e) {
+    const int c = atoi(e);
     return c < 1 ? 1 : c > 32 ? 32 : c;
-  }();
-  return v;
+  }
+  const size_t c = nr >> 19;
+  return c < 2 ? 2 : c > 16 ? 16 : (int)c;
 }
 
 // One host-buffer join with the three legs overlapped.  A join's pairs depend on all of S but
@@ -82,10 +88,10 @@ int join_u64_host_chunked(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, cons
                           size_t ns, uint32_t* h_out_r, uint32_t* h_out_s, size_t cap,
                           uint64_t* h_num_pairs, uint64_t* d_r, uint64_t* d_s, int* done) {
   *done = 0;
-  const int chunks = host_chunks_from_env();
+  const int chunks = host_chunks_for(nr);
   hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, 0);
   const char* e = getenv("HMJ_JOIN_UNIFORM");
-  const bool eligible = chunks > 1 && p.levels != 0 && nr >= ((size_t)chunks << 16) && ns > 0 &&
+  const bool eligible = chunks > 1 && p.levels != 0 && nr >= ((size_t)chunks << 16) && nr >= (size_t(1) << 19) && ns > 0 &&
                         !(e && atoi(e) == 0) && !ctx->hash_order;
   HMJ_TRY(ensure_copy_streams(ctx, (size_t)chunks + 2));
   cudaStream_t st = ctx->stream, cin = ctx->copy_in, cout = ctx->copy_out;
