@@ -386,7 +386,7 @@ bucket_join_table_kernel(const BJArgs A) {
     const uint4 nil = make_uint4(nil2, nil2, nil2, nil2);
     for (int i = tid; i < TBL * 2 / 16; i += BJ_THREADS) t4[i] = nil;
     uint4* n4 = reinterpret_cast<uint4*>(s_nxt);
-    for (int i = tid; i < BJ_CAP * 4 / 16; i += BJ_THREADS) n4[i] = nil;   // low half = NIL is what counts
+    for (int i = tid; i < (int)((ns + 3u) / 4u); i += BJ_THREADS) n4[i] = nil;  // S positions only; low half = NIL is what counts
   }
   __syncthreads();
   {
@@ -501,15 +501,17 @@ bucket_join_table_kernel(const BJArgs A) {
   }
   const uint32_t tile_total = F + E;
   if (tile_total == 0) return;
-  // room for the bucket's pairs: one atomicAdd on the global pair counter
+  // room for the bucket's pairs: one atomicAdd on the global pair counter.  Its round trip is
+  // needed first by the stores of the further matches; without any (unique keys in S) it hides
+  // behind the staging of the first matches and is read at the barrier that ends the staging.
   if (tid == 0) s_tmp[40] = atomicAdd(reinterpret_cast<unsigned long long*>(A.total),
                                       (unsigned long long)tile_total);
-  __syncthreads();
-  const uint64_t gbase = s_tmp[40];
-  if (gbase + tile_total > A.cap) return;  // does not fit: the host re-runs with the exact size
   // ---- further matches (duplicate keys in S): straight from the chain walk, behind the firsts
   if (E) {
-    uint64_t off = gbase + F + e_off;
+    __syncthreads();
+    const uint64_t gbase_e = s_tmp[40];
+    if (gbase_e + tile_total > A.cap) return;  // does not fit: the host re-runs with the exact size
+    uint64_t off = gbase_e + F + e_off;
 #pragma unroll
     for (int k = 0; k < BJ_ITEMS; ++k) {
       if (cnt[k] > 1) {
@@ -546,6 +548,8 @@ bucket_join_table_kernel(const BJArgs A) {
     }
   }
   __syncthreads();
+  const uint64_t gbase = s_tmp[40];
+  if (gbase + tile_total > A.cap) return;  // does not fit: the host re-runs with the exact size
   for (uint32_t i = tid; i < F; i += BJ_THREADS) {
     A.out_r[gbase + i] = s_or[swz(i)];
     A.out_s[gbase + i] = s_os[swz(i)];
