@@ -95,6 +95,7 @@ SIGNATURES = {
     "hmj_partition_pairs": (_I, [_P, _P, _P, _SZ, _I, _P, _P, _P]),
     "hmj_partition_pairs_base": (_I, [_P, _P, _P, C.c_uint32, _SZ, _I, _P, _P, _P]),
     "hmj_partition_pairs_noalloc": (_I, [_P, _P, _P, C.c_uint32, _SZ, _I, _P, _P, _P]),
+    "hmj_debug_plan_from_sample": (_I, [_P, C.c_uint32, _SZ, _SZ, _P]),
     "hmj_set_profiling": (_I, [_P, _I]),
     "hmj_partition_counts_host": (_I, [_P, _P, _SZ, _I, _P]),
     "hmj_hashjoin_build_probe": (_I, [_P, _RELP, _RELP, _P, _P, _U64P, _U64P]),

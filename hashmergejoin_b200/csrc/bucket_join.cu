@@ -674,6 +674,96 @@ sample_keys_kernel(const uint64_t* __restrict__ r, size_t nr, const uint64_t* __
 }
 }  // namespace
 
+// The plan a sample asks for (host only; tests/test_plan_from_sample.py drives it without a GPU
+// through hmj_debug_plan_from_sample).  h = per_side evenly spaced hashes of R, then of S.
+//  * prefix: the top bits all sampled hashes share are skipped (and checked by level 1);
+//  * density: when the hashes under the prefix fill only a part [lo, hi] of the range -- dense
+//    ids 0..N-1 with N not a power of two, identity-hashed -- a region of the filled part holds
+//    range / (hi - lo + 1) times its even share.  The plan then provides for n * density rows
+//    (bucket count, level-1 regions).  Only for at most one row per key value (the 2^12 values of
+//    a final bucket must fit its slots) and density <= 4;
+//  * skew: a level-1 region with more than its share (x density) + 50 % + 64 of a side's sample.
+void hmj_plan_from_sample(const uint64_t* h, uint32_t per_side, size_t nr, size_t ns,
+                          hmj_uniform_plan* p, bool skewed_side[2]) {
+  skewed_side[0] = skewed_side[1] = false;
+  const size_t n_side[2] = {nr, ns};
+  uint64_t diff = 0, lo[2] = {~0ull, ~0ull}, hi[2] = {0, 0};
+  for (uint32_t i = 0; i < 2 * per_side; ++i) diff |= h[i] ^ h[0];
+  int skip = diff ? __builtin_clzll(diff) : 64;
+  const size_t n_plan = nr > ns ? nr : ns;
+  if (hmj_uniform_plan_for(n_plan, 0).levels == 0) return;  // (*p stays the caller's)
+  // how much of the range under the prefix the keys fill, per side
+  const long double range = ldexpl(1.0L, 64 - skip);
+  long double dens[2] = {1.0L, 1.0L}, density = 1.0L, rows_per_value = 0.0L;
+  // (only under a shared prefix: hashes that use all 64 bits are not looked at again -- this runs
+  // inside every sampled join)
+  for (int side = 0; side < 2 && skip > 0; ++side) {
+    const uint64_t* hs = h + (size_t)side * per_side;
+    uint64_t l = ~0ull, m = 0;
+    for (uint32_t i = 0; i < per_side; ++i) {
+      const uint64_t v = hs[i];
+      l = v < l ? v : l;
+      m = v > m ? v : m;
+    }
+    lo[side] = l;
+    hi[side] = m;
+    const long double span = (long double)(hi[side] - lo[side]) + 1.0L;
+    dens[side] = range / span;
+    if (dens[side] > density) density = dens[side];
+    if ((long double)n_side[side] / span > rows_per_value) rows_per_value = (long double)n_side[side] / span;
+  }
+  size_t n_eff = n_plan;
+  if (density > 1.001L && density <= 4.0L && rows_per_value <= 1.001L &&
+      (long double)n_plan * density < 2147483648.0L) {
+    long double want = (long double)n_plan * density;
+    if (want > range) want = range;  // (<= one row per value: the sample's span is a hair short)
+    n_eff = (size_t)ceill(want);
+  } else {
+    density = 1.0L;
+    dens[0] = dens[1] = 1.0L;
+  }
+  hmj_uniform_plan q = hmj_uniform_plan_for(n_eff, 0);
+  if (q.levels == 0) return;
+  if (skip > 64 - q.qb - 12) skip = 64 - q.qb - 12;
+  if (skip > 0) {
+    q = hmj_uniform_plan_for(n_eff, skip);
+    if (q.levels == 0) {
+      *p = q;
+      return;
+    }
+    q.check_prefix = true;
+    q.prefix = h[0] >> (64 - skip);
+  }
+  q.density = (double)density;
+  // share of the sample per level-1 region
+  uint32_t hist[2][512] = {};
+  const int shift = 64 - q.skip - q.bits[0];
+  const uint32_t mask = (1u << q.bits[0]) - 1;
+  for (int side = 0; side < 2; ++side) {
+    const uint64_t* hs = h + (size_t)side * per_side;
+    uint32_t* hh = hist[side];
+    for (uint32_t i = 0; i < per_side; ++i) hh[(uint32_t)(hs[i] >> shift) & mask]++;
+  }
+  for (int side = 0; side < 2; ++side) {
+    const uint32_t expect = (uint32_t)((long double)(per_side >> q.bits[0]) * dens[side]);
+    for (uint32_t b = 0; b <= mask; ++b)
+      if (hist[side][b] > expect + expect / 2 + 64) skewed_side[side] = true;
+  }
+  *p = q;
+}
+
+extern "C" int hmj_debug_plan_from_sample(const uint64_t* h_sample, uint32_t per_side, size_t nr,
+                                          size_t ns, int64_t* out10) {
+  hmj_uniform_plan p = hmj_uniform_plan_for(nr > ns ? nr : ns, 0);
+  bool sk[2];
+  hmj_plan_from_sample(h_sample, per_side, nr, ns, &p, sk);
+  out10[0] = p.levels; out10[1] = p.bits[0]; out10[2] = p.bits[1]; out10[3] = p.qb; out10[4] = p.skip;
+  out10[5] = p.cap_seg; out10[6] = p.check_prefix; out10[7] = (int64_t)p.prefix;
+  out10[8] = (int64_t)llround((p.density > 1.0 ? p.density : 1.0) * 1e6);
+  out10[9] = (sk[0] ? 1 : 0) | (sk[1] ? 2 : 0);
+  return 0;
+}
+
 // Looks at 32768 evenly spaced hashes of each relation before anything is moved:
 //  * top bits that every sampled hash of BOTH relations shares (identity-hashed dense integer keys
 //    0..N-1 share their upper 64 - log2(N) bits) are skipped by the bucket plan, so such keys cut
@@ -700,31 +790,12 @@ int hmj_sample_plan(hmj_ctx* ctx, const uint64_t* r_hash, size_t nr, const uint6
   uint64_t* h = ctx->sample_host.data();
   HMJ_CUDA(ctx, cudaMemcpyAsync(h, d_sample, 2 * SAMPLE_PER_SIDE * 8, cudaMemcpyDeviceToHost, st));
   HMJ_CUDA(ctx, cudaStreamSynchronize(st));
-  uint64_t diff = 0;
-  for (uint32_t i = 0; i < 2 * SAMPLE_PER_SIDE; ++i) diff |= h[i] ^ h[0];
-  int skip = diff ? __builtin_clzll(diff) : 64;
-  const size_t n_plan = nr > ns ? nr : ns;
-  hmj_uniform_plan q = hmj_uniform_plan_for(n_plan, 0);
-  if (q.levels == 0) return HMJ_OK;
-  if (skip > 64 - q.qb - 12) skip = 64 - q.qb - 12;
-  if (skip > 0) {
-    q = hmj_uniform_plan_for(n_plan, skip);
-    q.check_prefix = true;
-    q.prefix = h[0] >> (64 - skip);
-  }
-  // share of the sample per level-1 region
-  uint32_t hist[2][512] = {};
-  const int shift = 64 - q.skip - q.bits[0];
-  const uint32_t mask = (1u << q.bits[0]) - 1;
-  for (uint32_t i = 0; i < 2 * SAMPLE_PER_SIDE; ++i) hist[i / SAMPLE_PER_SIDE][(uint32_t)(h[i] >> shift) & mask]++;
-  const uint32_t expect = SAMPLE_PER_SIDE >> q.bits[0];
+  bool sk[2] = {false, false};
+  hmj_plan_from_sample(h, SAMPLE_PER_SIDE, nr, ns, p, sk);
   for (int side = 0; side < 2; ++side) {
-    ctx->sample_skewed[side] = false;
-    for (uint32_t b = 0; b <= mask; ++b)
-      if (hist[side][b] > expect + expect / 2 + 64) ctx->sample_skewed[side] = true;
-    if (ctx->sample_skewed[side]) *skewed = 1;
+    ctx->sample_skewed[side] = sk[side];
+    if (sk[side]) *skewed = 1;
   }
-  *p = q;
   return HMJ_OK;
 }
 

@@ -633,7 +633,7 @@ int hmj_uniform_scatter(hmj_ctx* ctx, const uint64_t* keys_in, const uint32_t* v
   const uint32_t regions1 = 1u << p.bits[0], buckets = 1u << p.qb;
   uint32_t cap1 = 0;
   if (p.levels == 2) {
-    const double avg1 = (double)n / (double)regions1;
+    const double avg1 = (double)n * (p.density > 1.0 ? p.density : 1.0) / (double)regions1;
     cap1 = ((uint32_t)(avg1 + 8.0 * sqrt(avg1) + 64.0) + 255u) & ~255u;
   }
   // scratch words: [flag, tile counters: 8 words][level-1 cursors][final cursors][final offsets + 1]

@@ -217,6 +217,10 @@ struct hmj_uniform_plan {
   // against `prefix` and voids the attempt when one differs
   bool check_prefix;
   uint64_t prefix;
+  // > 1 (sample): the keys fill only 1/density of the range under the prefix, evenly -- dense ids
+  // 0..N-1 with N not a power of two.  A region then holds n * density / regions rows and the
+  // bucket count was chosen for n * density rows.  0 or 1: the rows spread over the whole range.
+  double density;
 };
 struct hmj_uniform_buckets {
   uint64_t* keys;     // bucket b at [b * cap_seg ...)
@@ -248,6 +252,9 @@ int hmj_bucket_join_run(hmj_ctx* ctx, int kind, const hmj_uniform_buckets& R,
                         int* ok);
 int hmj_sample_plan(hmj_ctx* ctx, const uint64_t* r_hash, size_t nr, const uint64_t* s_hash,
                     size_t ns, hmj_uniform_plan* p, int* skewed);
+// the host half of hmj_sample_plan: h = per_side evenly spaced hashes of R, then of S
+void hmj_plan_from_sample(const uint64_t* h, uint32_t per_side, size_t nr, size_t ns,
+                          hmj_uniform_plan* p, bool skewed_side[2]);
 int hmj_sort_uniform_try(hmj_ctx* ctx, const uint64_t* keys_in, size_t n, uint32_t iota_base,
                          uint64_t* keys_out, uint32_t* vals_out, int* ok);
 int hmj_impl_join_sorted(hmj_ctx* ctx, const hmj_relation* r, const hmj_relation* s,

@@ -140,9 +140,13 @@ int join_u64_host_chunked(hmj_ctx* ctx, const uint64_t* h_rkeys, size_t nr, cons
     p = skewed ? hmj_uniform_plan() : p;
     if (p.levels != 0 && (nr > ns ? nr : ns) != (n0 > ns ? n0 : ns)) {
       // (the sample planned for chunk 0's size: keep its prefix, take the bucket count of the join)
-      hmj_uniform_plan q = hmj_uniform_plan_for(nr > ns ? nr : ns, p.skip);
+      const double dens = p.density > 1.0 ? p.density : 1.0;
+      double want = (double)(nr > ns ? nr : ns) * dens;
+      if (dens > 1.0 && want > ldexp(1.0, 64 - p.skip)) want = ldexp(1.0, 64 - p.skip);  // one row per value at most
+      hmj_uniform_plan q = hmj_uniform_plan_for((size_t)ceil(want), p.skip);
       q.check_prefix = p.check_prefix;
       q.prefix = p.prefix;
+      q.density = p.density;
       p = q;
     }
     if (p.levels == 0) {

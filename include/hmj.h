@@ -346,6 +346,16 @@ int hmj_get_timings(hmj_ctx* ctx, hmj_timings* out);
  * kernel. */
 int hmj_set_profiling(hmj_ctx* ctx, int on);
 
+/* ---- test aid (host only, needs no GPU) ------------------------------------------------
+ * The bucket plan the join derives from a sample of both relations' hashes (bucket_join.cu,
+ * hmj_plan_from_sample; the counterpart of the reference's choice of the partition width,
+ * radix_hash.h:38-57, made from the data instead of from the row count alone).  h_sample:
+ * per_side evenly spaced hashes of R, then per_side of S.  out10 = levels, bits[0], bits[1],
+ * total bucket bits, skipped prefix bits, slots per bucket, prefix checked (0/1), prefix,
+ * density x 1e6, skew verdict (bit 0: R, bit 1: S). */
+int hmj_debug_plan_from_sample(const uint64_t* h_sample, uint32_t per_side, size_t nr, size_t ns,
+                               int64_t* out10);
+
 #ifdef __cplusplus
 }
 #endif

@@ -790,6 +790,34 @@ def test_join_dense_integer_keys_take_the_bucket_path(ctx):
     assert np.unique(out_r).size == n - 1
 
 
+def test_join_dense_keys_of_any_count_take_the_bucket_path(ctx):
+    # ids 0..N-1 with N not a power of two fill only N / 2^k of the range under their prefix: the
+    # sample measures that density and the plan provides for it (bucket count, level-1 regions)
+    rng = np.random.default_rng(31)
+    for n, base in ((5_000_000, 0), (3 << 21, 1 << 40), ((1 << 22) + 1000, 0), (4_500_000, (1 << 23) - 2_000_000)):
+        rk = rng.permutation(n).astype(np.uint64) + np.uint64(base)
+        sk = rng.permutation(n).astype(np.uint64) + np.uint64(base)
+        m = ctx.join_u64(dev(rk), dev(sk))
+        tm = ctx.timings()
+        assert tm["bucket_join"] == 1 and tm["sort_passes"] == 0 and tm["sort_fallbacks"] == 0, (n, base, tm)
+        _check_pairs_1to1(rk, sk, *ctx.join_result_to_host(m))
+    # a probe side that is a third of the ids, spread over the range
+    n = 6_000_000
+    rk = rng.permutation(n).astype(np.uint64)
+    sk = rng.choice(n, size=n // 3, replace=False).astype(np.uint64)
+    m = ctx.join_u64(dev(rk), dev(sk))
+    assert m == sk.size and ctx.timings()["bucket_join"] == 1
+    out_r, out_s = ctx.join_result_to_host(m)
+    assert np.array_equal(rk[out_r], sk[out_s]) and np.unique(out_s).size == m
+    # through the host entry (chunks of R): 3M dense ids
+    n = 3 << 20
+    rk, sk = rng.permutation(n).astype(np.uint64), rng.permutation(n).astype(np.uint64)
+    o_r, o_s = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+    assert ctx.join_u64_host(rk, sk, o_r, o_s) == n
+    assert ctx.timings()["bucket_join"] == 1 and ctx.timings()["scatter_levels"] > 4, "dense keys left the chunked plan"
+    _check_pairs_1to1(rk, sk, o_r, o_s)
+
+
 def test_join_skewed_keys_skip_the_scatter_attempt(ctx, oracle):
     # a Zipf-distributed integer relation: the sample sees the head key's region at several times
     # its share, so no bucket scatter is attempted at all
@@ -861,7 +889,7 @@ def test_host_join_in_chunks_and_its_fallbacks(ctx, oracle):
     assert np.unique(w).size == 3 * n
     # dense keys 0..N-1 through the host entry: the sample of S and of R's first chunk finds the
     # shared prefix, so the chunked plan (not the copy-join-copy fallback) runs
-    # (a power-of-two range: 0..3M-1 would leave a quarter of the buckets empty and overfill the rest)
+    # (a power-of-two range here; other counts: test_join_dense_keys_of_any_count_take_the_bucket_path)
     rng = np.random.default_rng(21)
     nd = 1 << 22
     dk_r, dk_s = rng.permutation(nd).astype(np.uint64), rng.permutation(nd).astype(np.uint64)
